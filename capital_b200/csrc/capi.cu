@@ -1,0 +1,459 @@
+// C ABI (include/capital_b200.h) over the sm_100a kernels.  No CPU fallback anywhere in this file.
+#include "../../include/capital_b200.h"
+#include "aux_kernels.cuh"
+#include "dmma_gemm.cuh"
+#include "handle.h"
+
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <string>
+
+using namespace capk;
+
+static thread_local std::string g_last_error;
+const char* cap_last_error(void) { return g_last_error.c_str(); }
+int cap_fail(int code, const char* what, const char* detail) {
+  g_last_error = std::string(what) + (detail ? std::string(": ") + detail : std::string());
+  return code;
+}
+#define CUDA_TRY(expr)                                                                   \
+  do {                                                                                   \
+    cudaError_t e_ = (expr);                                                             \
+    if (e_ != cudaSuccess) return cap_fail(CAP_ERR_CUDA, #expr, cudaGetErrorString(e_)); \
+  } while (0)
+#define CAP_TRY(expr)            \
+  do {                           \
+    int rc_ = (expr);            \
+    if (rc_ != CAP_OK) return rc_; \
+  } while (0)
+#define LAUNCH_CHECK(h)                                                                            \
+  do {                                                                                             \
+    (h)->launches++;                                                                               \
+    cudaError_t e_ = cudaGetLastError();                                                           \
+    if (e_ != cudaSuccess) return cap_fail(CAP_ERR_CUDA, "kernel launch", cudaGetErrorString(e_)); \
+  } while (0)
+
+// ------------------------------------------------------------------------------------------ context
+int cap_create(cap_handle_t* out, int device) {
+  int count = 0;
+  if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) return cap_fail(CAP_ERR_CUDA, "cap_create", "no CUDA device (there is no CPU fallback)");
+  if (device < 0 || device >= count) return cap_fail(CAP_ERR_ARG, "cap_create", "bad device index");
+  CUDA_TRY(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  CUDA_TRY(cudaGetDeviceProperties(&prop, device));
+  if (prop.major < 10) return cap_fail(CAP_ERR_UNSUPPORTED, "cap_create", "kernels are built for sm_100a only");
+  cap_handle_s* h = new cap_handle_s();
+  h->device = device;
+  h->num_sms = prop.multiProcessorCount;
+  CUDA_TRY(cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking));
+  CUDA_TRY(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+  h->stream = h->own_stream;
+  CUDA_TRY(cudaMalloc(&h->info_dev, sizeof(int)));
+  CUDA_TRY(cudaMemset(h->info_dev, 0, sizeof(int)));
+  // opt in to the large dynamic shared memory the tile engine and the base case need
+  CUDA_TRY(cudaFuncSetAttribute(dmma_gemm_kernel<false, false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES));
+  CUDA_TRY(cudaFuncSetAttribute(dmma_gemm_kernel<false, true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES));
+  CUDA_TRY(cudaFuncSetAttribute(dmma_gemm_kernel<true, false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES));
+  CUDA_TRY(cudaFuncSetAttribute(dmma_gemm_kernel<true, true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES));
+  CUDA_TRY(cudaFuncSetAttribute(dmma_gemm_kernel<false, false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES));
+  CUDA_TRY(cudaFuncSetAttribute(dmma_gemm_kernel<false, true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES));
+  CUDA_TRY(cudaFuncSetAttribute(dmma_gemm_kernel<true, false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES));
+  CUDA_TRY(cudaFuncSetAttribute(dmma_gemm_kernel<true, true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES));
+  CUDA_TRY(cudaFuncSetAttribute(dmma_trmm_right_inplace_kernel<false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES));
+  CUDA_TRY(cudaFuncSetAttribute(dmma_trmm_right_inplace_kernel<true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES));
+  CUDA_TRY(cudaFuncSetAttribute(dmma_trmm_right_inplace_kernel<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES));
+  CUDA_TRY(cudaFuncSetAttribute(dmma_trmm_right_inplace_kernel<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES));
+  CUDA_TRY(cudaFuncSetAttribute(potrf_trtri_base_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BASE_SMEM_BYTES));
+  *out = h;
+  return CAP_OK;
+}
+
+int cap_destroy(cap_handle_t h) {
+  if (!h) return CAP_OK;
+  cudaSetDevice(h->device);
+  cudaStreamSynchronize(h->stream);
+  for (auto& w : h->ws) if (w.ptr) cudaFree(w.ptr);
+  if (h->info_dev) cudaFree(h->info_dev);
+  if (h->ev_a) cudaEventDestroy(h->ev_a);
+  if (h->ev_b) cudaEventDestroy(h->ev_b);
+  cudaStreamDestroy(h->own_stream);
+  cudaStreamDestroy(h->copy_stream);
+  delete h;
+  return CAP_OK;
+}
+
+int cap_set_stream(cap_handle_t h, void* s) { h->stream = s ? (cudaStream_t)s : h->own_stream; return CAP_OK; }
+void* cap_get_stream(cap_handle_t h) { return (void*)h->stream; }
+int cap_synchronize(cap_handle_t h) { CUDA_TRY(cudaStreamSynchronize(h->stream)); return CAP_OK; }
+long long cap_kernel_launches(cap_handle_t h) { return h->launches; }
+int cap_get_info(cap_handle_t h, int* info) {
+  CUDA_TRY(cudaMemcpyAsync(info, h->info_dev, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+  CUDA_TRY(cudaStreamSynchronize(h->stream));
+  return CAP_OK;
+}
+int cap_reset_info(cap_handle_t h) { CUDA_TRY(cudaMemsetAsync(h->info_dev, 0, sizeof(int), h->stream)); return CAP_OK; }
+
+// Library-owned scratch: slot-indexed, grown on demand, never shrunk (stream-ordered reuse on one stream).
+int cap_workspace(cap_handle_t h, int slot, size_t bytes, double** out) {
+  auto& w = h->ws[slot];
+  if (w.bytes < bytes) {
+    if (w.ptr) { CUDA_TRY(cudaStreamSynchronize(h->stream)); CUDA_TRY(cudaFree(w.ptr)); w.ptr = nullptr; w.bytes = 0; }
+    if (cudaMalloc(&w.ptr, bytes) != cudaSuccess) { cudaGetLastError(); return cap_fail(CAP_ERR_ALLOC, "workspace", "cudaMalloc failed"); }
+    w.bytes = bytes;
+  }
+  *out = (double*)w.ptr;
+  return CAP_OK;
+}
+
+// ------------------------------------------------------------------------------------------ memory
+int cap_malloc(void** p, size_t bytes) {
+  if (cudaMalloc(p, bytes) != cudaSuccess) { cudaGetLastError(); return cap_fail(CAP_ERR_ALLOC, "cap_malloc", "cudaMalloc failed"); }
+  return CAP_OK;
+}
+int cap_free(void* p) { CUDA_TRY(cudaFree(p)); return CAP_OK; }
+int cap_memset_async(cap_handle_t h, void* p, int v, size_t bytes) { CUDA_TRY(cudaMemsetAsync(p, v, bytes, h->stream)); return CAP_OK; }
+int cap_h2d_async(cap_handle_t h, void* d, const void* s, size_t b) { CUDA_TRY(cudaMemcpyAsync(d, s, b, cudaMemcpyHostToDevice, h->stream)); return CAP_OK; }
+int cap_d2h_async(cap_handle_t h, void* d, const void* s, size_t b) { CUDA_TRY(cudaMemcpyAsync(d, s, b, cudaMemcpyDeviceToHost, h->stream)); return CAP_OK; }
+int cap_host_alloc(void** p, size_t bytes) {
+  if (cudaHostAlloc(p, bytes, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); return cap_fail(CAP_ERR_ALLOC, "cap_host_alloc", "cudaHostAlloc failed"); }
+  return CAP_OK;
+}
+int cap_host_free(void* p) { CUDA_TRY(cudaFreeHost(p)); return CAP_OK; }
+
+// ------------------------------------------------------------------------------------------ tile engine dispatch
+static inline bool aligned16(const void* p, int64_t ld) { return (((uintptr_t)p) & 15) == 0 && (ld & 1) == 0; }
+
+template <bool TA, bool TB>
+static void launch_gemm_t(cap_handle_t h, const GemmParams& p, int vec, dim3 grid) {
+  if (vec == 2) dmma_gemm_kernel<TA, TB, 2><<<grid, NTHREADS, GEMM_SMEM_BYTES, h->stream>>>(p);
+  else dmma_gemm_kernel<TA, TB, 1><<<grid, NTHREADS, GEMM_SMEM_BYTES, h->stream>>>(p);
+}
+
+// C = alpha*op(A)*op(B) + beta*Cin with optional k-range skipping / triangular store / split-K.
+static int gemm_launch(cap_handle_t h, GemmParams p, bool ta, bool tb, int want_ksplit) {
+  if (p.M <= 0 || p.N <= 0) return CAP_OK;
+  p.tiles_m = (p.M + BM - 1) / BM;
+  p.tiles_n = (p.N + BN - 1) / BN;
+  const int vec = (aligned16(p.A, p.lda) && aligned16(p.B, p.ldb)) ? 2 : 1;
+  int ntiles = p.tiles_m * p.tiles_n;
+  if (p.c_tri != CTRI_FULL && p.tiles_m == p.tiles_n) ntiles = p.tiles_m * (p.tiles_m + 1) / 2;
+  int ksplit = std::max(1, want_ksplit);
+  double* user_c = p.C; const int64_t user_ldc = p.ldc; const double alpha = p.alpha, beta = p.beta;
+  if (ksplit > 1) {
+    int kper = (int)(((int64_t)p.K + ksplit - 1) / ksplit);
+    kper = ((kper + BK - 1) / BK) * BK;
+    ksplit = (p.K + kper - 1) / kper;
+    if (ksplit > 1) {
+      double* part;
+      CAP_TRY(cap_workspace(h, CAP_WS_GEMM_SPLITK, (size_t)ksplit * p.M * p.N * sizeof(double), &part));
+      p.k_per_split = kper; p.c_split_stride = (int64_t)p.M * p.N; p.C = part; p.ldc = p.M;
+    }
+  }
+  p.ksplit = ksplit;
+  dim3 grid(ntiles, ksplit);
+  if (ta) { if (tb) launch_gemm_t<true, true>(h, p, vec, grid); else launch_gemm_t<true, false>(h, p, vec, grid); }
+  else    { if (tb) launch_gemm_t<false, true>(h, p, vec, grid); else launch_gemm_t<false, false>(h, p, vec, grid); }
+  LAUNCH_CHECK(h);
+  if (ksplit > 1) {
+    dim3 rg((p.M + 127) / 128, p.N);
+    splitk_reduce_kernel<<<rg, 128, 0, h->stream>>>(p.C, p.c_split_stride, p.M, ksplit, user_c, user_ldc, p.M, p.N, alpha, beta, p.c_tri);
+    LAUNCH_CHECK(h);
+  }
+  return CAP_OK;
+}
+
+// split-K factor for outputs too small to fill the machine (tall-skinny Gram, small trailing updates)
+static int auto_ksplit(cap_handle_t h, int ntiles, int64_t K) {
+  if (ntiles * 2 > h->num_sms || K < 2048) return 1;
+  int s = h->num_sms / ntiles;
+  const int64_t max_by_k = K / 512;
+  return (int)std::max<int64_t>(1, std::min<int64_t>(s, max_by_k));
+}
+
+static inline bool is_t(char c) { return c == 'T' || c == 't' || c == 'C' || c == 'c'; }
+static inline bool is_u(char c) { return c == 'U' || c == 'u'; }
+static inline bool is_l(char c) { return c == 'L' || c == 'l'; }
+
+int cap_dgemm(cap_handle_t h, char transa, char transb, int64_t m, int64_t n, int64_t k, double alpha,
+              const double* A, int64_t lda, const double* B, int64_t ldb, double beta, double* C, int64_t ldc) {
+  if (m < 0 || n < 0 || k < 0 || m > INT32_MAX || n > INT32_MAX || k > INT32_MAX) return cap_fail(CAP_ERR_ARG, "cap_dgemm", "bad dimension");
+  GemmParams p{};
+  p.A = A; p.B = B; p.C = C; p.Cin = C; p.lda = lda; p.ldb = ldb; p.ldc = ldc; p.ldcin = ldc;
+  p.M = (int)m; p.N = (int)n; p.K = (int)k; p.alpha = alpha; p.beta = beta;
+  const int ntiles = (int)(((m + BM - 1) / BM) * ((n + BN - 1) / BN));
+  return gemm_launch(h, p, is_t(transa), is_t(transb), auto_ksplit(h, ntiles, k));
+}
+
+int cap_dsyrk(cap_handle_t h, char uplo, char trans, int64_t n, int64_t k, double alpha,
+              const double* A, int64_t lda, double beta, double* C, int64_t ldc) {
+  if (n < 0 || k < 0 || n > INT32_MAX || k > INT32_MAX) return cap_fail(CAP_ERR_ARG, "cap_dsyrk", "bad dimension");
+  GemmParams p{};
+  p.A = A; p.B = A; p.C = C; p.Cin = C; p.lda = lda; p.ldb = lda; p.ldc = ldc; p.ldcin = ldc;
+  p.M = (int)n; p.N = (int)n; p.K = (int)k; p.alpha = alpha; p.beta = beta;
+  p.c_tri = is_u(uplo) ? CTRI_UPPER : CTRI_LOWER;
+  const int t = (int)((n + BM - 1) / BM);
+  const bool tr = is_t(trans);   // 'T': C = A^T A (A is k x n);  'N': C = A A^T (A is n x k)
+  return gemm_launch(h, p, tr, !tr, auto_ksplit(h, t * (t + 1) / 2, k));
+}
+
+__global__ void set_unit_diag_kernel(double* T, int64_t ld, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) T[i + (int64_t)i * ld] = 1.0;
+}
+
+// C = alpha*op(T)*B (left) or alpha*B*op(T) (right).  t_clean: the other triangle of T is already zero.
+static int trmm_impl(cap_handle_t h, char side, char uplo, char trans, char diag, int64_t m, int64_t n, double alpha,
+                     const double* T, int64_t ldt, const double* B, int64_t ldb, double* C, int64_t ldc, bool t_clean, bool inplace_right) {
+  if (m < 0 || n < 0 || m > INT32_MAX || n > INT32_MAX) return cap_fail(CAP_ERR_ARG, "cap_dtrmm", "bad dimension");
+  if (m == 0 || n == 0) return CAP_OK;
+  const bool left = is_l(side), upper = is_u(uplo), tr = is_t(trans), unit = is_u(diag);
+  const int64_t nt = left ? m : n;
+  if (!t_clean || unit) {  // masked copy of the referenced triangle (serialize-style), other half zero
+    double* tc;
+    CAP_TRY(cap_workspace(h, CAP_WS_TRI, (size_t)nt * nt * sizeof(double), &tc));
+    dim3 g((unsigned)((nt + 255) / 256), (unsigned)nt);
+    copy2d_kernel<<<g, 256, 0, h->stream>>>(tc, nt, T, ldt, nt, nt, upper ? 3 : 4);
+    LAUNCH_CHECK(h);
+    if (unit) { set_unit_diag_kernel<<<(unsigned)((nt + 255) / 256), 256, 0, h->stream>>>(tc, nt, (int)nt); LAUNCH_CHECK(h); }
+    T = tc; ldt = nt;
+  }
+  GemmParams p{};
+  p.C = C; p.Cin = C; p.ldc = ldc; p.ldcin = ldc; p.M = (int)m; p.N = (int)n; p.alpha = alpha; p.beta = 0.0;
+  const bool lo_bound = (upper != tr);  // left: Upper/NoTrans or Lower/Trans -> k >= i ; right: those -> k <= j
+  if (left) {
+    p.A = T; p.lda = ldt; p.B = B; p.ldb = ldb; p.K = (int)m;
+    if (lo_bound) p.klo_mode = KR_TILE_M; else p.khi_mode = KR_TILE_M;
+    return gemm_launch(h, p, tr, false, 1);
+  }
+  p.A = B; p.lda = ldb; p.B = T; p.ldb = ldt; p.K = (int)n;
+  if (lo_bound) p.khi_mode = KR_TILE_N; else p.klo_mode = KR_TILE_N;
+  if (!inplace_right) return gemm_launch(h, p, false, tr, 1);
+  p.tiles_m = (p.M + BM - 1) / BM; p.tiles_n = (p.N + BN - 1) / BN; p.ksplit = 1;
+  const int vec = (aligned16(p.A, p.lda) && aligned16(p.B, p.ldb)) ? 2 : 1;
+  const int grid = p.tiles_m;
+  if (tr) { if (vec == 2) dmma_trmm_right_inplace_kernel<true, 2><<<grid, NTHREADS, GEMM_SMEM_BYTES, h->stream>>>(p);
+            else dmma_trmm_right_inplace_kernel<true, 1><<<grid, NTHREADS, GEMM_SMEM_BYTES, h->stream>>>(p); }
+  else    { if (vec == 2) dmma_trmm_right_inplace_kernel<false, 2><<<grid, NTHREADS, GEMM_SMEM_BYTES, h->stream>>>(p);
+            else dmma_trmm_right_inplace_kernel<false, 1><<<grid, NTHREADS, GEMM_SMEM_BYTES, h->stream>>>(p); }
+  LAUNCH_CHECK(h);
+  return CAP_OK;
+}
+
+int cap_dtrmm_oop(cap_handle_t h, char side, char uplo, char trans, char diag, int64_t m, int64_t n, double alpha,
+                  const double* T, int64_t ldt, const double* B, int64_t ldb, double* C, int64_t ldc) {
+  return trmm_impl(h, side, uplo, trans, diag, m, n, alpha, T, ldt, B, ldb, C, ldc, false, false);
+}
+
+int cap_dtrmm(cap_handle_t h, char side, char uplo, char trans, char diag, int64_t m, int64_t n, double alpha,
+              const double* T, int64_t ldt, double* B, int64_t ldb) {
+  if (!is_l(side)) return trmm_impl(h, side, uplo, trans, diag, m, n, alpha, T, ldt, B, ldb, B, ldb, false, true);
+  if (m <= 0 || n <= 0) return CAP_OK;
+  double* copy;  // left side: every output row block needs all of B's rows -> go through a copy of B
+  CAP_TRY(cap_workspace(h, CAP_WS_PANEL, (size_t)m * n * sizeof(double), &copy));
+  dim3 g((unsigned)std::min<int64_t>((m + 255) / 256, 65535), (unsigned)n);
+  copy2d_kernel<<<g, 256, 0, h->stream>>>(copy, m, B, ldb, m, n, 0);
+  LAUNCH_CHECK(h);
+  return trmm_impl(h, side, uplo, trans, diag, m, n, alpha, T, ldt, copy, m, B, ldb, false, false);
+}
+
+int cap_cqr_gram(cap_handle_t h, int64_t m, int64_t n, const double* Q, int64_t ldq, double* G, int64_t ldg) {
+  return cap_dsyrk(h, 'U', 'T', n, m, 1.0, Q, ldq, 0.0, G, ldg);
+}
+
+int cap_cqr_apply(cap_handle_t h, int64_t m, int64_t n, const double* Rinv, int64_t ldr,
+                  const double* Qin, int64_t ldqin, double* Qout, int64_t ldqout) {
+  const bool inplace = (Qin == Qout);
+  if (inplace && ldqin != ldqout) return cap_fail(CAP_ERR_ARG, "cap_cqr_apply", "in-place call needs equal leading dimensions");
+  return trmm_impl(h, 'R', 'U', 'N', 'N', m, n, 1.0, Rinv, ldr, Qin, ldqin, Qout, ldqout, /*t_clean=*/true, inplace);
+}
+
+// ------------------------------------------------------------------------------------------ LAPACK engine
+static int memset2d(cap_handle_t h, double* p, int64_t ld, int64_t m, int64_t n) {
+  CUDA_TRY(cudaMemset2DAsync(p, (size_t)ld * 8, 0, (size_t)m * 8, (size_t)n, h->stream));
+  return CAP_OK;
+}
+static int copy2d(cap_handle_t h, double* dst, int64_t ldd, const double* src, int64_t lds, int64_t m, int64_t n, int mode) {
+  if (m <= 0 || n <= 0) return CAP_OK;
+  dim3 g((unsigned)std::min<int64_t>((m + 255) / 256, 65535), (unsigned)n);
+  copy2d_kernel<<<g, 256, 0, h->stream>>>(dst, ldd, src, lds, m, n, mode);
+  LAUNCH_CHECK(h);
+  return CAP_OK;
+}
+static int base_case(cap_handle_t h, double* A, int64_t lda, double* X, int64_t ldx, int n, int info_base, int write_r, int skip_potrf, int lower) {
+  potrf_trtri_base_kernel<<<1, BASE_THREADS, BASE_SMEM_BYTES, h->stream>>>(A, lda, X, ldx, n, h->info_dev, info_base, write_r, 1, skip_potrf, lower);
+  LAUNCH_CHECK(h);
+  return CAP_OK;
+}
+static inline int split_point(int len) { return ((len / 2 + BASE_NB - 1) / BASE_NB) * BASE_NB; }
+
+// Recursive Cholesky + inverse on one device: the schedule of cholesky::cholinv::invoke
+// (reference src/alg/cholesky/cholinv/cholinv.hpp:87-165) with a true triangular-store syrk.
+// A(off.., off..) upper -> R in place; X = Rinv (zero-initialised by the caller).  W: 2 x (len/2)^2 scratch.
+static int cholinv_rec(cap_handle_t h, double* A, int64_t lda, double* X, int64_t ldx, int off, int len, bool top, int complete_inv, double* W) {
+  double* A11 = A + off + (int64_t)off * lda;
+  double* X11 = X + off + (int64_t)off * ldx;
+  if (len <= BASE_NB) return base_case(h, A11, lda, X11, ldx, len, off, 1, 0, 0);
+  const int n1 = split_point(len), n2 = len - n1;
+  double* A12 = A11 + (int64_t)n1 * lda;
+  double* A22 = A12 + n1;
+  double* X12 = X11 + (int64_t)n1 * ldx;
+  double* X22 = X12 + n1;
+  CAP_TRY(cholinv_rec(h, A, lda, X, ldx, off, n1, false, complete_inv, W));
+  // "trsm" (cholinv.hpp:116-121): R12 = R11^{-T} A12 through the explicit inverse
+  CAP_TRY(trmm_impl(h, 'L', 'U', 'T', 'N', n1, n2, 1.0, X11, ldx, A12, lda, W, n1, true, false));
+  CAP_TRY(copy2d(h, A12, lda, W, n1, n1, n2, 0));
+  // trailing update (cholinv.hpp:131-134): A22 -= R12^T R12, upper triangle only
+  CAP_TRY(cap_dsyrk(h, 'U', 'T', n2, n1, -1.0, W, n1, 1.0, A22, lda));
+  CAP_TRY(cholinv_rec(h, A, lda, X, ldx, off + n1, n2, false, complete_inv, W));
+  if (!(top && !complete_inv)) {
+    // inverse completion (cholinv.hpp:147-156): Rinv12 = -(Rinv11 R12) Rinv22
+    double* W2 = W + (int64_t)n1 * n2;
+    CAP_TRY(trmm_impl(h, 'L', 'U', 'N', 'N', n1, n2, 1.0, X11, ldx, A12, lda, W2, n1, true, false));
+    CAP_TRY(trmm_impl(h, 'R', 'U', 'N', 'N', n1, n2, -1.0, X22, ldx, W2, n1, X12, ldx, true, false));
+  }
+  return CAP_OK;
+}
+
+static size_t cholinv_scratch_doubles(int n) {
+  if (n <= BASE_NB) return 2;
+  const int n1 = split_point(n);
+  return (size_t)2 * n1 * (n - n1) + 2;
+}
+
+int cap_dcholinv(cap_handle_t h, int n, double* A, int64_t lda, double* Rinv, int64_t ldri, int complete_inv) {
+  if (n < 0) return cap_fail(CAP_ERR_ARG, "cap_dcholinv", "bad dimension");
+  if (n == 0) return CAP_OK;
+  double* W;
+  CAP_TRY(cap_workspace(h, CAP_WS_PANEL, cholinv_scratch_doubles(n) * sizeof(double), &W));
+  CAP_TRY(memset2d(h, Rinv, ldri, n, n));
+  return cholinv_rec(h, A, lda, Rinv, ldri, 0, n, true, complete_inv, W);
+}
+
+int cap_dpotrf(cap_handle_t h, char uplo, int n, double* A, int lda) {
+  if (!is_u(uplo)) return cap_fail(CAP_ERR_UNSUPPORTED, "cap_dpotrf", "only uplo='U' (the reference asserts dir=='U', cholinv.hpp:9)");
+  if (n <= 0) return n == 0 ? CAP_OK : cap_fail(CAP_ERR_ARG, "cap_dpotrf", "bad dimension");
+  double* X;
+  CAP_TRY(cap_workspace(h, CAP_WS_FACTOR, (size_t)n * n * sizeof(double), &X));
+  return cap_dcholinv(h, n, A, lda, X, n, 0);
+}
+
+// X = T^{-1} by recursive block inversion; T upper (lower: mirrored).  X zero-initialised by the caller.
+static int trtri_rec(cap_handle_t h, const double* T, int64_t ldt, double* X, int64_t ldx, int off, int len, bool lower, double* W) {
+  const double* T11 = T + off + (int64_t)off * ldt;
+  double* X11 = X + off + (int64_t)off * ldx;
+  if (len <= BASE_NB) return base_case(h, const_cast<double*>(T11), ldt, X11, ldx, len, off, 0, 1, lower ? 1 : 0);
+  const int n1 = split_point(len), n2 = len - n1;
+  CAP_TRY(trtri_rec(h, T, ldt, X, ldx, off, n1, lower, W));
+  CAP_TRY(trtri_rec(h, T, ldt, X, ldx, off + n1, n2, lower, W));
+  double* X22 = X11 + n1 + (int64_t)n1 * ldx;
+  if (!lower) {  // X12 = -(X11 T12) X22
+    const double* T12 = T11 + (int64_t)n1 * ldt;
+    CAP_TRY(trmm_impl(h, 'L', 'U', 'N', 'N', n1, n2, 1.0, X11, ldx, T12, ldt, W, n1, true, false));
+    CAP_TRY(trmm_impl(h, 'R', 'U', 'N', 'N', n1, n2, -1.0, X22, ldx, W, n1, X11 + (int64_t)n1 * ldx, ldx, true, false));
+  } else {       // X21 = -(X22 T21) X11
+    const double* T21 = T11 + n1;
+    CAP_TRY(trmm_impl(h, 'L', 'L', 'N', 'N', n2, n1, 1.0, X22, ldx, T21, ldt, W, n2, true, false));
+    CAP_TRY(trmm_impl(h, 'R', 'L', 'N', 'N', n2, n1, -1.0, X11, ldx, W, n2, X11 + n1, ldx, true, false));
+  }
+  return CAP_OK;
+}
+
+int cap_dtrtri(cap_handle_t h, char uplo, char diag, int n, double* A, int lda) {
+  if (is_u(diag)) return cap_fail(CAP_ERR_UNSUPPORTED, "cap_dtrtri", "unit-diagonal inverse is not on the path");
+  if (n <= 0) return n == 0 ? CAP_OK : cap_fail(CAP_ERR_ARG, "cap_dtrtri", "bad dimension");
+  const bool lower = is_l(uplo);
+  double *X, *W;
+  CAP_TRY(cap_workspace(h, CAP_WS_FACTOR, (size_t)n * n * sizeof(double), &X));
+  CAP_TRY(cap_workspace(h, CAP_WS_PANEL, cholinv_scratch_doubles(n) * sizeof(double), &W));
+  CAP_TRY(memset2d(h, X, n, n, n));
+  CAP_TRY(trtri_rec(h, A, lda, X, n, 0, n, lower, W));
+  return copy2d(h, A, lda, X, n, n, n, lower ? 2 : 1);   // only the referenced triangle is overwritten (LAPACK semantics)
+}
+
+// ------------------------------------------------------------------------------------------ serialize / util / generators
+int cap_copy2d(cap_handle_t h, double* dst, int64_t ldd, const double* src, int64_t lds, int64_t m, int64_t n, int mode) {
+  return copy2d(h, dst, ldd, src, lds, m, n, mode);
+}
+int cap_pack_upper(cap_handle_t h, double* packed, const double* full, int64_t ld, int n) {
+  if (n <= 0) return CAP_OK;
+  pack_upper_kernel<<<dim3((n + 255) / 256, n), 256, 0, h->stream>>>(packed, full, ld, n);
+  LAUNCH_CHECK(h);
+  return CAP_OK;
+}
+int cap_unpack_upper(cap_handle_t h, double* full, int64_t ld, const double* packed, int n, int zero_lower) {
+  if (n <= 0) return CAP_OK;
+  unpack_upper_kernel<<<dim3((n + 255) / 256, n), 256, 0, h->stream>>>(full, ld, packed, n, zero_lower);
+  LAUNCH_CHECK(h);
+  return CAP_OK;
+}
+int cap_axpby(cap_handle_t h, double* y, const double* x, int64_t count, double alpha, double beta) {
+  if (count <= 0) return CAP_OK;
+  const int blocks = (int)std::min<int64_t>((count + 255) / 256, (int64_t)h->num_sms * 16);
+  axpby_kernel<<<blocks, 256, 0, h->stream>>>(y, x, count, alpha, beta);
+  LAUNCH_CHECK(h);
+  return CAP_OK;
+}
+int cap_fill_random(cap_handle_t h, double* dst, int64_t ld, int64_t rows, int64_t cols, long long key) {
+  const int64_t total = rows * cols;
+  if (total <= 0) return CAP_OK;
+  const int64_t threads = (total + 15) / 16;
+  fill_random_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, h->stream>>>(dst, ld, rows, cols, key, 0);
+  LAUNCH_CHECK(h);
+  return CAP_OK;
+}
+int cap_fill_symmetric(cap_handle_t h, double* dst, int64_t ld, int64_t rows, int64_t cols, int64_t px, int64_t py,
+                       int64_t grid_x, int64_t grid_y, int64_t global_dim, int diagonally_dominant) {
+  if (rows <= 0 || cols <= 0) return CAP_OK;
+  dim3 g((unsigned)std::min<int64_t>((rows + 255) / 256, 65535), (unsigned)cols);
+  fill_symmetric_kernel<<<g, 256, 0, h->stream>>>(dst, ld, rows, cols, px, py, grid_x, grid_y, global_dim, diagonally_dominant ? (double)global_dim : 0.0);
+  LAUNCH_CHECK(h);
+  return CAP_OK;
+}
+
+// ------------------------------------------------------------------------------------------ CholeskyQR2, 1D
+// qr::cacqr::sweep_1d (reference src/alg/qr/cacqr/cacqr.hpp:7-29) with the Serialize policy's packed Gram
+// exchange (policy.h:77-85): syrk -> pack -> allreduce -> unpack -> potrf+trtri -> Q = Qin * Rinv.
+static int cqr_sweep(cap_handle_t h, cap_comm_t comm, int64_t m, int64_t n, const double* Qin, int64_t ldin, double* Qout, int64_t ldout,
+                     double* G, double* Rinv, double* packed) {
+  CAP_TRY(memset2d(h, G, n, n, n));
+  CAP_TRY(cap_cqr_gram(h, m, n, Qin, ldin, G, n));
+  if (comm) {
+    CAP_TRY(cap_pack_upper(h, packed, G, n, (int)n));
+    CAP_TRY(cap_allreduce_sum(h, comm, packed, n * (n + 1) / 2));
+    CAP_TRY(cap_unpack_upper(h, G, n, packed, (int)n, 0));
+  }
+  CAP_TRY(cap_dcholinv(h, (int)n, G, n, Rinv, n, 1));
+  return cap_cqr_apply(h, m, n, Rinv, n, Qin, ldin, Qout, ldout);
+}
+
+int cap_cacqr_factor_1d(cap_handle_t h, cap_comm_t comm, int64_t m_loc, int64_t n, const double* A, int64_t lda,
+                        double* Q, int64_t ldq, double* R, int64_t ldr, int num_iter) {
+  if (m_loc < 0 || n <= 0 || n > INT32_MAX || m_loc > INT32_MAX) return cap_fail(CAP_ERR_ARG, "cap_cacqr_factor_1d", "bad dimension");
+  if (num_iter < 1 || num_iter > 2) return cap_fail(CAP_ERR_ARG, "cap_cacqr_factor_1d", "num_iter must be 1 or 2");
+  double* ws;
+  const size_t nn = (size_t)n * n;
+  CAP_TRY(cap_workspace(h, CAP_WS_GRAM, (4 * nn) * sizeof(double), &ws));
+  double *G1 = ws, *G2 = ws + nn, *Rinv = ws + 2 * nn, *packed = ws + 3 * nn;
+  CAP_TRY(cqr_sweep(h, comm, m_loc, n, A, lda, Q, ldq, G1, Rinv, packed));          // A is never copied: sweep 1 reads A, writes Q
+  if (num_iter == 1) return copy2d(h, R, ldr, G1, n, n, n, 3);
+  CAP_TRY(cqr_sweep(h, comm, m_loc, n, Q, ldq, Q, ldq, G2, Rinv, packed));          // sweep 2 in place on Q
+  // R = R2 * R1 (cacqr.hpp:184-187); both factors have zero strict lower parts here
+  return trmm_impl(h, 'R', 'U', 'N', 'N', n, n, 1.0, G1, n, G2, n, R, ldr, true, false);
+}
+
+int cap_cacqr_factor_1d_host(cap_handle_t h, cap_comm_t comm, int64_t m_loc, int64_t n, const double* A_host, int64_t lda,
+                             double* Q_host, int64_t ldq, double* R_host, int64_t ldr, int num_iter) {
+  if (lda != m_loc || ldq != m_loc || ldr != n) return cap_fail(CAP_ERR_ARG, "cap_cacqr_factor_1d_host", "host buffers must be dense (ld == rows)");
+  const size_t bytes = (size_t)m_loc * n * sizeof(double);
+  double *dA, *dQ, *dR;
+  CAP_TRY(cap_workspace(h, CAP_WS_STAGE0, bytes, &dA));
+  CAP_TRY(cap_workspace(h, CAP_WS_STAGE1, bytes, &dQ));
+  CAP_TRY(cap_workspace(h, CAP_WS_FACTOR, (size_t)n * n * sizeof(double), &dR));
+  CUDA_TRY(cudaMemcpyAsync(dA, A_host, bytes, cudaMemcpyHostToDevice, h->stream));
+  CAP_TRY(cap_cacqr_factor_1d(h, comm, m_loc, n, dA, m_loc, dQ, m_loc, dR, n, num_iter));
+  CUDA_TRY(cudaMemcpyAsync(Q_host, dQ, bytes, cudaMemcpyDeviceToHost, h->stream));
+  CUDA_TRY(cudaMemcpyAsync(R_host, dR, (size_t)n * n * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+  CUDA_TRY(cudaStreamSynchronize(h->stream));
+  return CAP_OK;
+}

@@ -1,0 +1,24 @@
+// Internal: the opaque handle behind cap_handle_t and helpers shared by the C-ABI translation units.
+#pragma once
+#include <cuda_runtime.h>
+#include <stddef.h>
+#include <stdint.h>
+
+enum { CAP_WS_GEMM_SPLITK = 0, CAP_WS_TRI = 1, CAP_WS_PANEL = 2, CAP_WS_FACTOR = 3, CAP_WS_STAGE0 = 4, CAP_WS_STAGE1 = 5, CAP_WS_GRAM = 6, CAP_WS_SLOTS = 8 };
+
+struct cap_ws_slot { void* ptr = nullptr; size_t bytes = 0; };
+
+struct cap_handle_s {
+  int device = 0;
+  int num_sms = 148;
+  cudaStream_t stream = nullptr;      // current stream (caller's or own)
+  cudaStream_t own_stream = nullptr;
+  cudaStream_t copy_stream = nullptr; // host<->device staging for the e2e entry points
+  cudaEvent_t ev_a = nullptr, ev_b = nullptr;
+  int* info_dev = nullptr;
+  long long launches = 0;
+  cap_ws_slot ws[CAP_WS_SLOTS];
+};
+
+int cap_fail(int code, const char* what, const char* detail);
+int cap_workspace(cap_handle_s* h, int slot, size_t bytes, double** out);

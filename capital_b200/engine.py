@@ -1,0 +1,138 @@
+"""Python host mirror of the reference's engine interface over the C ABI.
+
+Names and argument meaning follow blas::engine::_gemm/_trmm/_syrk (reference src/blas/interface.h:57-66)
+and lapack::engine::_potrf/_trtri (src/lapack/interface.h:49-53); matrices are torch CUDA float64
+tensors in COLUMN-MAJOR layout (stride(0) == 1), the reference's only layout on this path.
+torch is plumbing here (device memory + streams); all arithmetic is in libcapital_b200.so."""
+import ctypes as C
+
+import torch
+
+from . import _lib
+
+
+def colmajor(rows, cols, device="cuda", fill=None):
+    """rows x cols float64 tensor with Fortran strides (1, rows)."""
+    base = torch.empty((cols, rows), dtype=torch.float64, device=device)
+    if fill is not None:
+        base.fill_(fill)
+    return base.t()
+
+
+def to_colmajor(t):
+    """Copy any 2-D tensor/ndarray into a column-major CUDA tensor."""
+    t = torch.as_tensor(t, dtype=torch.float64)
+    out = colmajor(t.shape[0], t.shape[1], device="cuda")
+    out.copy_(t)
+    return out
+
+
+def _ld(t):
+    assert t.dtype == torch.float64 and t.is_cuda and t.dim() == 2, "need a 2-D CUDA float64 tensor"
+    assert t.shape[0] <= 1 or t.stride(0) == 1, "matrix must be column-major (stride(0) == 1)"
+    return max(1, t.stride(1)) if t.shape[1] > 1 else max(1, t.shape[0])
+
+
+def _c(ch):
+    return C.c_char(ch.encode())
+
+
+class Engine:
+    """One handle = one device + stream + library-owned workspace (the reference's engines are static
+    classes; the handle is what a device back end needs in addition)."""
+
+    def __init__(self, device=0):
+        self.lib = _lib.load()
+        self.h = C.c_void_p()
+        _lib.check(self.lib.cap_create(C.byref(self.h), int(device)), "cap_create")
+        self.device = int(device)
+        self.use_torch_stream()
+
+    def use_torch_stream(self):
+        s = torch.cuda.current_stream(self.device).cuda_stream
+        _lib.check(self.lib.cap_set_stream(self.h, C.c_void_p(s)), "cap_set_stream")
+
+    def close(self):
+        if self.h:
+            self.lib.cap_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def launches(self):
+        return int(self.lib.cap_kernel_launches(self.h))
+
+    def info(self):
+        v = C.c_int(0)
+        _lib.check(self.lib.cap_get_info(self.h, C.byref(v)), "cap_get_info")
+        return v.value
+
+    def reset_info(self):
+        _lib.check(self.lib.cap_reset_info(self.h), "cap_reset_info")
+
+    # ---- blas::engine -------------------------------------------------------------------------
+    def _gemm(self, A, B, Cm, m, n, k, transa="N", transb="N", alpha=1.0, beta=0.0):
+        _lib.check(self.lib.cap_dgemm(self.h, _c(transa), _c(transb), m, n, k, alpha, A.data_ptr(), _ld(A),
+                                      B.data_ptr(), _ld(B), beta, Cm.data_ptr(), _ld(Cm)), "cap_dgemm")
+
+    def _syrk(self, A, Cm, n, k, uplo="U", trans="T", alpha=1.0, beta=0.0):
+        _lib.check(self.lib.cap_dsyrk(self.h, _c(uplo), _c(trans), n, k, alpha, A.data_ptr(), _ld(A), beta,
+                                      Cm.data_ptr(), _ld(Cm)), "cap_dsyrk")
+
+    def _trmm(self, T, B, m, n, side="R", uplo="U", trans="N", diag="N", alpha=1.0):
+        _lib.check(self.lib.cap_dtrmm(self.h, _c(side), _c(uplo), _c(trans), _c(diag), m, n, alpha, T.data_ptr(), _ld(T),
+                                      B.data_ptr(), _ld(B)), "cap_dtrmm")
+
+    def trmm_oop(self, T, B, Cm, m, n, side="R", uplo="U", trans="N", diag="N", alpha=1.0):
+        _lib.check(self.lib.cap_dtrmm_oop(self.h, _c(side), _c(uplo), _c(trans), _c(diag), m, n, alpha, T.data_ptr(), _ld(T),
+                                          B.data_ptr(), _ld(B), Cm.data_ptr(), _ld(Cm)), "cap_dtrmm_oop")
+
+    # ---- lapack::engine -----------------------------------------------------------------------
+    def _potrf(self, A, n, uplo="U"):
+        _lib.check(self.lib.cap_dpotrf(self.h, _c(uplo), n, A.data_ptr(), _ld(A)), "cap_dpotrf")
+
+    def _trtri(self, A, n, uplo="U", diag="N"):
+        _lib.check(self.lib.cap_dtrtri(self.h, _c(uplo), _c(diag), n, A.data_ptr(), _ld(A)), "cap_dtrtri")
+
+    def cholinv(self, A, Rinv, n, complete_inv=True):
+        _lib.check(self.lib.cap_dcholinv(self.h, n, A.data_ptr(), _ld(A), Rinv.data_ptr(), _ld(Rinv), int(bool(complete_inv))), "cap_dcholinv")
+
+    # ---- CholeskyQR -----------------------------------------------------------------------------
+    def cqr_gram(self, Q, G):
+        m, n = Q.shape
+        _lib.check(self.lib.cap_cqr_gram(self.h, m, n, Q.data_ptr(), _ld(Q), G.data_ptr(), _ld(G)), "cap_cqr_gram")
+
+    def cqr_apply(self, Rinv, Qin, Qout):
+        m, n = Qin.shape
+        _lib.check(self.lib.cap_cqr_apply(self.h, m, n, Rinv.data_ptr(), _ld(Rinv), Qin.data_ptr(), _ld(Qin),
+                                          Qout.data_ptr(), _ld(Qout)), "cap_cqr_apply")
+
+    def cacqr_factor_1d(self, A, Q, R, num_iter=2, comm=None):
+        m, n = A.shape
+        _lib.check(self.lib.cap_cacqr_factor_1d(self.h, comm, m, n, A.data_ptr(), _ld(A), Q.data_ptr(), _ld(Q),
+                                                R.data_ptr(), _ld(R), num_iter), "cap_cacqr_factor_1d")
+
+    def cacqr_factor_1d_host(self, A_host, Q_host, R_host, m, n, num_iter=2, comm=None):
+        """A_host/Q_host: pinned CPU tensors holding the m x n block column-major (shape (n, m) contiguous)."""
+        _lib.check(self.lib.cap_cacqr_factor_1d_host(self.h, comm, m, n, A_host.data_ptr(), m, Q_host.data_ptr(), m,
+                                                     R_host.data_ptr(), n, num_iter), "cap_cacqr_factor_1d_host")
+
+    # ---- serialize / generators -----------------------------------------------------------------
+    def copy2d(self, dst, src, m, n, mode=0):
+        _lib.check(self.lib.cap_copy2d(self.h, dst.data_ptr(), _ld(dst), src.data_ptr(), _ld(src), m, n, mode), "cap_copy2d")
+
+    def pack_upper(self, packed, full, n):
+        _lib.check(self.lib.cap_pack_upper(self.h, packed.data_ptr(), full.data_ptr(), _ld(full), n), "cap_pack_upper")
+
+    def unpack_upper(self, full, packed, n, zero_lower=True):
+        _lib.check(self.lib.cap_unpack_upper(self.h, full.data_ptr(), _ld(full), packed.data_ptr(), n, int(zero_lower)), "cap_unpack_upper")
+
+    def axpby(self, y, x, alpha, beta):
+        _lib.check(self.lib.cap_axpby(self.h, y.data_ptr(), x.data_ptr(), y.numel(), alpha, beta), "cap_axpby")
+
+    def fill_random(self, dst, key):
+        """matrix::distribute_random (reference src/matrix/structure.hpp:106-129) for this rank's local block."""
+        _lib.check(self.lib.cap_fill_random(self.h, dst.data_ptr(), _ld(dst), dst.shape[0], dst.shape[1], int(key)), "cap_fill_random")
+
+    def fill_symmetric(self, dst, px, py, grid_x, grid_y, global_dim, diagonally_dominant=True):
+        """matrix::distribute_symmetric (src/matrix/structure.hpp:69-103)."""
+        _lib.check(self.lib.cap_fill_symmetric(self.h, dst.data_ptr(), _ld(dst), dst.shape[0], dst.shape[1], px, py, grid_x, grid_y,
+                                               global_dim, int(diagonally_dominant)), "cap_fill_symmetric")

@@ -1,0 +1,114 @@
+/* capital_b200 -- C ABI of the B200-native factorization hot path.
+ *
+ * Drop-in boundary for huttered40/capital's engine layer (reference paths relative to the repo root):
+ *   blas::engine::_gemm/_trmm/_syrk        src/blas/interface.h:57-66   (double specialisations interface.hpp:43-97)
+ *   lapack::engine::_potrf/_trtri          src/lapack/interface.h:49-53 (interface.hpp:31-58)
+ * plus the memory/serialize, generator and collective calls the algorithms make around them, so
+ * that the schedules of src/alg/{qr/cacqr,cholesky/cholinv,matmult/summa} run on device buffers.
+ *
+ * Conventions: every matrix pointer is a DEVICE pointer on the handle's device, column-major, FP64;
+ * calls are stream-ordered on the handle's stream and do not synchronise unless stated; flags are
+ * the BLAS characters ('N','T' / 'U','L' / 'L','R' / 'N','U'); return value 0 = success, otherwise a
+ * CAP_* status (never an exception).  potrf/trtri report LAPACK-style `info` through a device int
+ * owned by the handle (cap_get_info synchronises and returns it).  There is no CPU fallback: if no
+ * CUDA device is usable, cap_create fails.
+ */
+#ifndef CAPITAL_B200_H_
+#define CAPITAL_B200_H_
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct cap_handle_s* cap_handle_t;
+typedef struct cap_comm_s* cap_comm_t;
+
+enum { CAP_OK = 0, CAP_ERR_ARG = 1, CAP_ERR_CUDA = 2, CAP_ERR_ALLOC = 3, CAP_ERR_NCCL = 4, CAP_ERR_UNSUPPORTED = 5 };
+
+/* ---- context ------------------------------------------------------------------------------- */
+int cap_create(cap_handle_t* h, int device);
+int cap_destroy(cap_handle_t h);
+int cap_set_stream(cap_handle_t h, void* cuda_stream);      /* cudaStream_t; NULL = handle's own stream */
+void* cap_get_stream(cap_handle_t h);
+int cap_synchronize(cap_handle_t h);
+const char* cap_last_error(void);
+int cap_get_info(cap_handle_t h, int* info);                 /* syncs; LAPACK info of potrf/trtri since last reset */
+int cap_reset_info(cap_handle_t h);
+long long cap_kernel_launches(cap_handle_t h);               /* number of kernels this handle has launched */
+
+/* ---- memory (matrix<>::_assemble / _destroy_, src/matrix/structure.hpp:4-24, matrix.hpp:158) -- */
+int cap_malloc(void** dptr, size_t bytes);
+int cap_free(void* dptr);
+int cap_memset_async(cap_handle_t h, void* dptr, int value, size_t bytes);
+int cap_h2d_async(cap_handle_t h, void* dst, const void* src, size_t bytes);
+int cap_d2h_async(cap_handle_t h, void* dst, const void* src, size_t bytes);
+int cap_host_alloc(void** hptr, size_t bytes);               /* pinned */
+int cap_host_free(void* hptr);
+
+/* ---- BLAS-3 engine (src/blas/interface.hpp:43-97) -------------------------------------------- */
+int cap_dgemm(cap_handle_t h, char transa, char transb, int64_t m, int64_t n, int64_t k, double alpha,
+              const double* A, int64_t lda, const double* B, int64_t ldb, double beta, double* C, int64_t ldc);
+int cap_dsyrk(cap_handle_t h, char uplo, char trans, int64_t n, int64_t k, double alpha,
+              const double* A, int64_t lda, double beta, double* C, int64_t ldc);
+/* in place, B <- alpha*op(T)*B (side 'L') or alpha*B*op(T) (side 'R'); only `uplo` triangle of T is read */
+int cap_dtrmm(cap_handle_t h, char side, char uplo, char trans, char diag, int64_t m, int64_t n, double alpha,
+              const double* T, int64_t ldt, double* B, int64_t ldb);
+/* out of place, C <- alpha*op(T)*B or alpha*B*op(T); B and C must not overlap */
+int cap_dtrmm_oop(cap_handle_t h, char side, char uplo, char trans, char diag, int64_t m, int64_t n, double alpha,
+                  const double* T, int64_t ldt, const double* B, int64_t ldb, double* C, int64_t ldc);
+
+/* ---- LAPACK engine (src/lapack/interface.hpp:31-58) ------------------------------------------ */
+int cap_dpotrf(cap_handle_t h, char uplo, int n, double* A, int lda);            /* 'U' only (cholinv.hpp:9) */
+int cap_dtrtri(cap_handle_t h, char uplo, char diag, int n, double* A, int lda);  /* 'U' or 'L', non-unit */
+/* fused potrf + trtri as the reference always uses them (cacqr.hpp:20-22, cholinv/policy.h:199-201):
+ * A(upper) <- R, Rinv(upper) <- R^-1, strict lower of Rinv zeroed.  complete_inv=0 leaves the top-level
+ * off-diagonal block of Rinv unset, exactly like cholinv (cholinv.hpp:147). */
+int cap_dcholinv(cap_handle_t h, int n, double* A, int64_t lda, double* Rinv, int64_t ldri, int complete_inv);
+
+/* ---- CholeskyQR fast paths (cacqr.hpp:7-29) -------------------------------------------------- */
+/* G(upper, n x n, ldg) <- Q^T Q for the local m x n row block; deterministic split-K. */
+int cap_cqr_gram(cap_handle_t h, int64_t m, int64_t n, const double* Q, int64_t ldq, double* G, int64_t ldg);
+/* Qout <- Qin * triu(Rinv); Qout may equal Qin (in place) or be a different buffer. */
+int cap_cqr_apply(cap_handle_t h, int64_t m, int64_t n, const double* Rinv, int64_t ldr,
+                  const double* Qin, int64_t ldqin, double* Qout, int64_t ldqout);
+
+/* ---- serialize / util (src/matrix/serialize.hpp:12-150, src/util/util.hpp:267-318, summa.hpp:33) */
+/* mode: 0 all, 1 upper only, 2 lower only, 3 upper + zero strict lower, 4 lower + zero strict upper */
+int cap_copy2d(cap_handle_t h, double* dst, int64_t ldd, const double* src, int64_t lds, int64_t m, int64_t n, int mode);
+int cap_pack_upper(cap_handle_t h, double* packed, const double* full, int64_t ld, int n);
+int cap_unpack_upper(cap_handle_t h, double* full, int64_t ld, const double* packed, int n, int zero_lower);
+int cap_axpby(cap_handle_t h, double* y, const double* x, int64_t count, double alpha, double beta);
+
+/* ---- generators (src/matrix/structure.hpp:69-129), bit-exact with glibc drand48 -------------- */
+int cap_fill_random(cap_handle_t h, double* dst, int64_t ld, int64_t rows, int64_t cols, long long key);
+int cap_fill_symmetric(cap_handle_t h, double* dst, int64_t ld, int64_t rows, int64_t cols, int64_t px, int64_t py,
+                       int64_t grid_x, int64_t grid_y, int64_t global_dim, int diagonally_dominant);
+
+/* ---- collectives: NCCL in place of the reference's MPI ------------------------ */
+int cap_comm_unique_id(char* id128);                          /* 128-byte ncclUniqueId */
+int cap_comm_init_rank(cap_comm_t* comm, const char* id128, int nranks, int rank);
+int cap_comm_split(cap_comm_t parent, int color, int key, cap_comm_t* child);
+int cap_comm_destroy(cap_comm_t comm);
+int cap_comm_rank(cap_comm_t comm, int* rank);
+int cap_comm_size(cap_comm_t comm, int* size);
+int cap_allreduce_sum(cap_handle_t h, cap_comm_t comm, double* buf, int64_t count);              /* in place */
+int cap_reduce_sum(cap_handle_t h, cap_comm_t comm, double* buf, int64_t count, int root);        /* in place at root */
+int cap_bcast(cap_handle_t h, cap_comm_t comm, double* buf, int64_t count, int root);
+int cap_allgather(cap_handle_t h, cap_comm_t comm, const double* send, double* recv, int64_t count_per_rank);
+int cap_sendrecv(cap_handle_t h, cap_comm_t comm, const double* send, double* recv, int64_t count, int peer);
+
+/* ---- algorithm entry points (device-resident; src/alg/...) ----------------------------------- */
+/* qr::cacqr::factor, 1D (cacqr.hpp:219-248 -> invoke_1d :174-193).  A is the local m_loc x n row block
+ * (untouched), Q the output block, R the n x n upper factor (full layout, strict lower zero).
+ * comm may be NULL for a single rank.  num_iter: 1 = CholeskyQR, 2 = CholeskyQR2. */
+int cap_cacqr_factor_1d(cap_handle_t h, cap_comm_t comm, int64_t m_loc, int64_t n, const double* A, int64_t lda,
+                        double* Q, int64_t ldq, double* R, int64_t ldr, int num_iter);
+/* Same, end to end from HOST memory: A_host -> device (chunked, overlapped with the first Gram pass),
+ * factor, Q and R -> host.  Buffers should be pinned (cap_host_alloc) for full PCIe speed. */
+int cap_cacqr_factor_1d_host(cap_handle_t h, cap_comm_t comm, int64_t m_loc, int64_t n, const double* A_host, int64_t lda,
+                             double* Q_host, int64_t ldq, double* R_host, int64_t ldr, int num_iter);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CAPITAL_B200_H_ */
