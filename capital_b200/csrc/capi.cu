@@ -83,7 +83,8 @@ int cap_destroy(cap_handle_t h) {
   return CAP_OK;
 }
 
-int cap_set_stream(cap_handle_t h, void* s) { h->stream = s ? (cudaStream_t)s : h->own_stream; return CAP_OK; }
+int cap_set_stream(cap_handle_t h, void* s) { h->stream = (cudaStream_t)s; return CAP_OK; }   // NULL = the legacy default stream
+int cap_use_own_stream(cap_handle_t h) { h->stream = h->own_stream; return CAP_OK; }
 void* cap_get_stream(cap_handle_t h) { return (void*)h->stream; }
 int cap_synchronize(cap_handle_t h) { CUDA_TRY(cudaStreamSynchronize(h->stream)); return CAP_OK; }
 long long cap_kernel_launches(cap_handle_t h) { return h->launches; }

@@ -28,7 +28,8 @@ enum { CAP_OK = 0, CAP_ERR_ARG = 1, CAP_ERR_CUDA = 2, CAP_ERR_ALLOC = 3, CAP_ERR
 /* ---- context ------------------------------------------------------------------------------- */
 int cap_create(cap_handle_t* h, int device);
 int cap_destroy(cap_handle_t h);
-int cap_set_stream(cap_handle_t h, void* cuda_stream);      /* cudaStream_t; NULL = handle's own stream */
+int cap_set_stream(cap_handle_t h, void* cuda_stream);      /* cudaStream_t; NULL = the legacy default stream */
+int cap_use_own_stream(cap_handle_t h);                     /* back to the handle's private non-blocking stream (the default) */
 void* cap_get_stream(cap_handle_t h);
 int cap_synchronize(cap_handle_t h);
 const char* cap_last_error(void);

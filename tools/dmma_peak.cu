@@ -28,7 +28,7 @@ int main() {
   double* out; cudaMalloc(&out, 8);
   cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
   const int iters = 20000;
-  for (int warps = 4; warps <= 32; warps *= 2) {
+  for (int warps = 4; warps <= 16; warps *= 2) {
     float best_m = 1e30f, best_f = 1e30f;
     for (int rep = 0; rep < 5; ++rep) {
       float ms;

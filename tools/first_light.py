@@ -47,9 +47,9 @@ for n in [64, 128, 200, 512, 1024, 2048]:
     R = torch.triu(A); Rref = torch.linalg.cholesky(torch.as_tensor(A_np, device="cuda")).t()
     print("cholinv", n, "R %.2e" % rel(R, Rref), "Rinv %.2e" % rel(X, torch.linalg.inv(Rref)), "info", E.info(), flush=True)
 n = 700
-Tn = np.triu(np.random.rand(n, n)) + n * np.eye(n); T = to_colmajor(Tn); E._trtri(T, n, "U", "N")
+Tn = np.triu(np.random.rand(n, n)) + n * np.eye(n); T = to_colmajor(Tn); E._trtri(T, n, "U", "N"); torch.cuda.synchronize()
 print("trtri U", "%.2e" % rel(torch.triu(T), torch.linalg.inv(torch.as_tensor(Tn, device="cuda"))))
-T = to_colmajor(Tn.T.copy()); E._trtri(T, n, "L", "N")
+T = to_colmajor(Tn.T.copy()); E._trtri(T, n, "L", "N"); torch.cuda.synchronize()
 print("trtri L", "%.2e" % rel(torch.tril(T), torch.linalg.inv(torch.as_tensor(Tn.T.copy(), device="cuda"))))
 
 # generators + CQR2 vs numpy oracle
