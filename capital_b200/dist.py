@@ -1,0 +1,71 @@
+"""One process per GPU: torch.distributed is the plumbing (rendezvous, id exchange, timing reduction);
+the data-path collectives are NCCL calls inside libcapital_b200.so (csrc/comm.cu).
+
+Sharding of the CholeskyQR path follows the reference's 1D layout (bench/qr/cacqr.cpp:32-34):
+matrix A(n, m, c=1, d=P) -- rows dealt cyclically, rank r owns ceil-divided rows and generates them
+with distribute_random(key = rank)."""
+import ctypes as C
+
+import torch
+import torch.distributed as dist
+
+
+def local_rows(m, ranks, rank):
+    """Rows of the m x n matrix owned by `rank` under the reference's cyclic deal; the local buffer has
+    ceil(m/P) rows (matrix.hpp:8-11), of which the last is zero padding on ranks past the remainder."""
+    padded = -(-m // ranks)
+    owned = padded if (m % ranks == 0 or rank < m % ranks) else padded - 1
+    return padded, owned
+
+
+def broadcast_bytes(payload, src=0):
+    """Broadcast a bytes object from `src` over the default process group (gloo or nccl)."""
+    n = torch.tensor([len(payload) if dist.get_rank() == src else 0], dtype=torch.int64)
+    dev = "cuda" if dist.get_backend() == "nccl" else "cpu"
+    n = n.to(dev); dist.broadcast(n, src)
+    buf = torch.zeros(int(n.item()), dtype=torch.uint8, device=dev)
+    if dist.get_rank() == src:
+        buf.copy_(torch.frombuffer(bytearray(payload), dtype=torch.uint8))
+    dist.broadcast(buf, src)
+    return bytes(buf.cpu().numpy().tobytes())
+
+
+def max_over_ranks(value):
+    """Device-timed milliseconds -> max over ranks (the reference's PMPI_Allreduce(MAX), bench/qr/cacqr.cpp:52)."""
+    if not dist.is_initialized() or dist.get_world_size() == 1:
+        return float(value)
+    dev = "cuda" if dist.get_backend() == "nccl" else "cpu"
+    t = torch.tensor([float(value)], dtype=torch.float64, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+class Comm:
+    """NCCL communicator owned by the C-ABI library (cap_comm_t), bootstrapped through torch.distributed."""
+
+    def __init__(self, engine):
+        self.lib = engine.lib
+        self.ptr = C.c_void_p()
+        self.rank, self.size = dist.get_rank(), dist.get_world_size()
+        ident = C.create_string_buffer(128)
+        if self.rank == 0:
+            from . import _lib
+            _lib.check(self.lib.cap_comm_unique_id(ident), "cap_comm_unique_id")
+        raw = broadcast_bytes(ident.raw, 0)
+        from . import _lib
+        _lib.check(self.lib.cap_comm_init_rank(C.byref(self.ptr), raw, self.size, self.rank), "cap_comm_init_rank")
+
+    def split(self, color, key):
+        from . import _lib
+        child = Comm.__new__(Comm)
+        child.lib, child.ptr = self.lib, C.c_void_p()
+        _lib.check(self.lib.cap_comm_split(self.ptr, color, key, C.byref(child.ptr)), "cap_comm_split")
+        r, s = C.c_int(), C.c_int()
+        self.lib.cap_comm_rank(child.ptr, C.byref(r)); self.lib.cap_comm_size(child.ptr, C.byref(s))
+        child.rank, child.size = r.value, s.value
+        return child
+
+    def close(self):
+        if self.ptr:
+            self.lib.cap_comm_destroy(self.ptr)
+            self.ptr = C.c_void_p()

@@ -37,6 +37,7 @@ static std::string g_prefix;
 static int g_rank = 0, g_size = 1;
 
 static void dump(const char* name, const T* p, size_t n) {
+  if (getenv("REF_NO_DUMP")) return;   // timing-only runs (bench.py cpu_baseline / --impl reference)
   std::string f = g_prefix + ".r" + std::to_string(g_rank) + "." + name + ".f64";
   FILE* fp = fopen(f.c_str(), "wb");
   if (!fp || fwrite(p, sizeof(T), n, fp) != n) { perror(f.c_str()); _exit(4); }
