@@ -62,12 +62,12 @@ def cpu_reference_rate(m_sample, n, cores):
 
 def reference_arm(args):
     """--impl reference: the reference's own CPU implementation of the path, all host cores, each
-    step one bounded sample (2^17 x 1024 of the 2^22 x 1024 workload)."""
+    step one bounded sample (2^19 x 1024 rows = one eighth of the 2^22 x 1024 workload)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
     cores = host_cores()
-    m_sample = 1 << 17
+    m_sample = 1 << 19
     rates, secs = [], []
     ranks = threads = 1
     for _ in range(max(1, args.steps)):
@@ -240,7 +240,7 @@ def ours_arm(args):
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         try:
             cores = host_cores()
-            m_sample = 1 << 17
+            m_sample = 1 << 19
             rate, ranks_c, threads_c, sec = cpu_reference_rate(m_sample, n, cores)
             cpu = {"value": rate, "unit": "TFLOP/s", "cores": ranks_c * threads_c, "kind": "reference", "seconds": sec,
                    "sample": "CholeskyQR2 %dx%d (1/%d of the rows), unmodified reference via oracle/_ref, %d minimpi ranks x %d OpenBLAS threads" % (
