@@ -2,6 +2,7 @@
 #include "../../include/capital_b200.h"
 #include "aux_kernels.cuh"
 #include "dmma_gemm.cuh"
+#include "dmma_tma_gemm.cuh"
 #include "handle.h"
 
 #include <algorithm>
@@ -65,6 +66,19 @@ int cap_create(cap_handle_t* out, int device) {
   CUDA_TRY(cudaFuncSetAttribute(dmma_trmm_right_inplace_kernel<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES));
   CUDA_TRY(cudaFuncSetAttribute(dmma_trmm_right_inplace_kernel<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES));
   CUDA_TRY(cudaFuncSetAttribute(potrf_trtri_base_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BASE_SMEM_BYTES));
+  CUDA_TRY(cudaFuncSetAttribute(dmma_tma_gemm_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, T_SMEM_BYTES));
+  CUDA_TRY(cudaFuncSetAttribute(dmma_tma_gemm_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, T_SMEM_BYTES));
+  CUDA_TRY(cudaFuncSetAttribute(dmma_tma_gemm_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, T_SMEM_BYTES));
+  CUDA_TRY(cudaFuncSetAttribute(dmma_tma_gemm_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, T_SMEM_BYTES));
+  {  // cuTensorMapEncodeTiled through the runtime (no link-time dependency on libcuda)
+    cudaDriverEntryPointQueryResult qres;
+    void* fn = nullptr;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres) != cudaSuccess || qres != cudaDriverEntryPointSuccess || !fn) {
+      cudaGetLastError();
+      return cap_fail(CAP_ERR_CUDA, "cap_create", "cuTensorMapEncodeTiled is not available from this driver");
+    }
+    h->encode_tiled = fn;
+  }
   *out = h;
   return CAP_OK;
 }
@@ -131,15 +145,63 @@ static void launch_gemm_t(cap_handle_t h, const GemmParams& p, int vec, dim3 gri
   else dmma_gemm_kernel<TA, TB, 1><<<grid, NTHREADS, GEMM_SMEM_BYTES, h->stream>>>(p);
 }
 
+// ---- TMA engine (dmma_tma_gemm.cuh) ----------------------------------------------------------
+typedef CUresult (*encode_tiled_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                    const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                    CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+// 2-D FP64 tensor map: dim0 = contiguous index (extent `inner`), dim1 strided by ld doubles (extent `outer`).
+static int make_map(cap_handle_t h, CUtensorMap* map, const double* base, int64_t inner, int64_t outer, int64_t ld, bool k_contig) {
+  cuuint64_t dims[2] = {(cuuint64_t)inner, (cuuint64_t)outer};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * 8};
+  cuuint32_t box[2] = {16u, k_contig ? 128u : 16u};
+  cuuint32_t estr[2] = {1u, 1u};
+  CUresult r = ((encode_tiled_fn)h->encode_tiled)(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, const_cast<double*>(base), dims, strides, box, estr,
+                                                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                                                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return cap_fail(CAP_ERR_CUDA, "cuTensorMapEncodeTiled", "tensor map rejected");
+  return CAP_OK;
+}
+
+static bool tma_eligible(cap_handle_t h, const GemmParams& p) {
+  return h->engine == 0 && p.K > 0 && aligned16(p.A, p.lda) && aligned16(p.B, p.ldb) &&
+         p.lda < (int64_t(1) << 36) && p.ldb < (int64_t(1) << 36);
+}
+
+// split-K factor: outputs too small to fill the machine (tall-skinny Gram, small trailing updates) are cut
+// into k-slabs.  Prefer a factor that makes the number of work units a multiple of the SM count (every
+// persistent CTA then gets the same number of units, and with the triangular enumeration the same mix of
+// diagonal and full tiles); otherwise one unit per SM.
+static int pick_ksplit(cap_handle_t h, int ntiles, int64_t K, bool persistent) {
+  if (ntiles * 2 > h->num_sms || K < 2048) return 1;
+  const int64_t max_by_k = std::max<int64_t>(1, K / 1024);
+  if (persistent) {
+    int a = ntiles, b = h->num_sms;
+    while (b) { int tmp = a % b; a = b; b = tmp; }
+    const int step = h->num_sms / a;                       // smallest s with ntiles*s % num_sms == 0
+    if (step <= max_by_k && (int64_t)ntiles * step <= (int64_t)16 * h->num_sms) return step;
+  }
+  return (int)std::max<int64_t>(1, std::min<int64_t>(h->num_sms / ntiles, max_by_k));
+}
+
+template <bool A_KC, bool B_KC>
+static void launch_tma_t(cap_handle_t h, const CUtensorMap& ma, const CUtensorMap& mb, const TmaGemmParams& tp, int grid) {
+  dmma_tma_gemm_kernel<A_KC, B_KC><<<grid, T_THREADS, T_SMEM_BYTES, h->stream>>>(ma, mb, tp);
+}
+
 // C = alpha*op(A)*op(B) + beta*Cin with optional k-range skipping / triangular store / split-K.
-static int gemm_launch(cap_handle_t h, GemmParams p, bool ta, bool tb, int want_ksplit) {
+// diag: DIAG_* of the triangular operand (its other triangle must hold zeros inside the diagonal blocks);
+// rowpanel: one CTA owns a whole 128-row block of C and walks its column tiles in the order that makes
+// B <- B*op(T) safe in place (also the balanced schedule for tall panels).
+static int gemm_launch(cap_handle_t h, GemmParams p, bool ta, bool tb, int want_ksplit, int diag = DIAG_NONE, bool rowpanel = false) {
   if (p.M <= 0 || p.N <= 0) return CAP_OK;
   p.tiles_m = (p.M + BM - 1) / BM;
   p.tiles_n = (p.N + BN - 1) / BN;
-  const int vec = (aligned16(p.A, p.lda) && aligned16(p.B, p.ldb)) ? 2 : 1;
-  int ntiles = p.tiles_m * p.tiles_n;
-  if (p.c_tri != CTRI_FULL && p.tiles_m == p.tiles_n) ntiles = p.tiles_m * (p.tiles_m + 1) / 2;
-  int ksplit = std::max(1, want_ksplit);
+  const bool tri_sq = (p.c_tri != CTRI_FULL && p.tiles_m == p.tiles_n);
+  int ntiles = tri_sq ? p.tiles_m * (p.tiles_m + 1) / 2 : p.tiles_m * p.tiles_n;
+  const bool tma = tma_eligible(h, p);
+  int ksplit = 1;
+  if (want_ksplit < 0) ksplit = pick_ksplit(h, ntiles, p.K, tma); else ksplit = std::max(1, want_ksplit);
   double* user_c = p.C; const int64_t user_ldc = p.ldc; const double alpha = p.alpha, beta = p.beta;
   if (ksplit > 1) {
     int kper = (int)(((int64_t)p.K + ksplit - 1) / ksplit);
@@ -152,10 +214,45 @@ static int gemm_launch(cap_handle_t h, GemmParams p, bool ta, bool tb, int want_
     }
   }
   p.ksplit = ksplit;
-  dim3 grid(ntiles, ksplit);
-  if (ta) { if (tb) launch_gemm_t<true, true>(h, p, vec, grid); else launch_gemm_t<true, false>(h, p, vec, grid); }
-  else    { if (tb) launch_gemm_t<false, true>(h, p, vec, grid); else launch_gemm_t<false, false>(h, p, vec, grid); }
-  LAUNCH_CHECK(h);
+  if (tma) {
+    CUtensorMap ma, mb;
+    // op(A): 'T' -> stored K x M, k contiguous; 'N' -> stored M x K, m contiguous.  op(B): 'N' -> stored K x N, k contiguous.
+    CAP_TRY(make_map(h, &ma, p.A, ta ? p.K : p.M, ta ? p.M : p.K, p.lda, ta));
+    CAP_TRY(make_map(h, &mb, p.B, tb ? p.N : p.K, tb ? p.K : p.N, p.ldb, !tb));
+    TmaGemmParams tp{};
+    tp.C = p.C; tp.Cin = p.Cin; tp.ldc = p.ldc; tp.ldcin = p.ldcin; tp.M = p.M; tp.N = p.N; tp.K = p.K;
+    tp.alpha = p.alpha; tp.beta = p.beta; tp.klo_mode = p.klo_mode; tp.khi_mode = p.khi_mode; tp.c_tri = p.c_tri;
+    tp.diag = (ksplit > 1) ? DIAG_NONE : diag;
+    tp.ksplit = ksplit; tp.k_per_split = p.k_per_split; tp.c_split_stride = p.c_split_stride;
+    tp.tiles_m = p.tiles_m; tp.tiles_n = p.tiles_n;
+    tp.subs = 1;
+    if (rowpanel) {
+      tp.sched = (p.khi_mode == KR_TILE_N) ? SCHED_ROWPANEL_DESC : SCHED_ROWPANEL_ASC;
+      tp.units = p.tiles_m; tp.subs = p.tiles_n;
+    } else if (tri_sq) { tp.sched = SCHED_TRI; tp.units = ntiles * ksplit; }
+    else { tp.sched = (p.khi_mode == KR_TILE_M) ? SCHED_TM_DESC : SCHED_RASTER; tp.units = ntiles * ksplit; }
+    tp.c_vec2 = (aligned16(tp.C, tp.ldc) && (beta == 0.0 || ksplit > 1 || aligned16(tp.Cin, tp.ldcin))) ? 1 : 0;
+    const int grid = std::min(tp.units, h->num_sms);
+    const bool akc = ta, bkc = !tb;
+    if (akc) { if (bkc) launch_tma_t<true, true>(h, ma, mb, tp, grid); else launch_tma_t<true, false>(h, ma, mb, tp, grid); }
+    else     { if (bkc) launch_tma_t<false, true>(h, ma, mb, tp, grid); else launch_tma_t<false, false>(h, ma, mb, tp, grid); }
+    LAUNCH_CHECK(h);
+  } else if (rowpanel) {
+    const int vec = (aligned16(p.A, p.lda) && aligned16(p.B, p.ldb)) ? 2 : 1;
+    const int grid = p.tiles_m;
+    if (ta) return cap_fail(CAP_ERR_ARG, "gemm_launch", "row-panel schedule needs op(A) = A");
+    if (tb) { if (vec == 2) dmma_trmm_right_inplace_kernel<true, 2><<<grid, NTHREADS, GEMM_SMEM_BYTES, h->stream>>>(p);
+              else dmma_trmm_right_inplace_kernel<true, 1><<<grid, NTHREADS, GEMM_SMEM_BYTES, h->stream>>>(p); }
+    else    { if (vec == 2) dmma_trmm_right_inplace_kernel<false, 2><<<grid, NTHREADS, GEMM_SMEM_BYTES, h->stream>>>(p);
+              else dmma_trmm_right_inplace_kernel<false, 1><<<grid, NTHREADS, GEMM_SMEM_BYTES, h->stream>>>(p); }
+    LAUNCH_CHECK(h);
+  } else {
+    const int vec = (aligned16(p.A, p.lda) && aligned16(p.B, p.ldb)) ? 2 : 1;
+    dim3 grid(ntiles, ksplit);
+    if (ta) { if (tb) launch_gemm_t<true, true>(h, p, vec, grid); else launch_gemm_t<true, false>(h, p, vec, grid); }
+    else    { if (tb) launch_gemm_t<false, true>(h, p, vec, grid); else launch_gemm_t<false, false>(h, p, vec, grid); }
+    LAUNCH_CHECK(h);
+  }
   if (ksplit > 1) {
     dim3 rg((p.M + 127) / 128, p.N);
     splitk_reduce_kernel<<<rg, 128, 0, h->stream>>>(p.C, p.c_split_stride, p.M, ksplit, user_c, user_ldc, p.M, p.N, alpha, beta, p.c_tri);
@@ -164,12 +261,10 @@ static int gemm_launch(cap_handle_t h, GemmParams p, bool ta, bool tb, int want_
   return CAP_OK;
 }
 
-// split-K factor for outputs too small to fill the machine (tall-skinny Gram, small trailing updates)
-static int auto_ksplit(cap_handle_t h, int ntiles, int64_t K) {
-  if (ntiles * 2 > h->num_sms || K < 2048) return 1;
-  int s = h->num_sms / ntiles;
-  const int64_t max_by_k = K / 512;
-  return (int)std::max<int64_t>(1, std::min<int64_t>(s, max_by_k));
+int cap_set_engine(cap_handle_t h, int engine) {
+  if (engine != 0 && engine != 1) return cap_fail(CAP_ERR_ARG, "cap_set_engine", "0 = auto, 1 = cp.async engine only");
+  h->engine = engine;
+  return CAP_OK;
 }
 
 static inline bool is_t(char c) { return c == 'T' || c == 't' || c == 'C' || c == 'c'; }
@@ -183,7 +278,8 @@ int cap_dgemm(cap_handle_t h, char transa, char transb, int64_t m, int64_t n, in
   p.A = A; p.B = B; p.C = C; p.Cin = C; p.lda = lda; p.ldb = ldb; p.ldc = ldc; p.ldcin = ldc;
   p.M = (int)m; p.N = (int)n; p.K = (int)k; p.alpha = alpha; p.beta = beta;
   const int ntiles = (int)(((m + BM - 1) / BM) * ((n + BN - 1) / BN));
-  return gemm_launch(h, p, is_t(transa), is_t(transb), auto_ksplit(h, ntiles, k));
+  (void)ntiles;
+  return gemm_launch(h, p, is_t(transa), is_t(transb), -1);
 }
 
 int cap_dsyrk(cap_handle_t h, char uplo, char trans, int64_t n, int64_t k, double alpha,
@@ -195,7 +291,8 @@ int cap_dsyrk(cap_handle_t h, char uplo, char trans, int64_t n, int64_t k, doubl
   p.c_tri = is_u(uplo) ? CTRI_UPPER : CTRI_LOWER;
   const int t = (int)((n + BM - 1) / BM);
   const bool tr = is_t(trans);   // 'T': C = A^T A (A is k x n);  'N': C = A A^T (A is n x k)
-  return gemm_launch(h, p, tr, !tr, auto_ksplit(h, t * (t + 1) / 2, k));
+  (void)t;
+  return gemm_launch(h, p, tr, !tr, -1);
 }
 
 __global__ void set_unit_diag_kernel(double* T, int64_t ld, int n) {
@@ -225,20 +322,13 @@ static int trmm_impl(cap_handle_t h, char side, char uplo, char trans, char diag
   if (left) {
     p.A = T; p.lda = ldt; p.B = B; p.ldb = ldb; p.K = (int)m;
     if (lo_bound) p.klo_mode = KR_TILE_M; else p.khi_mode = KR_TILE_M;
-    return gemm_launch(h, p, tr, false, 1);
+    return gemm_launch(h, p, tr, false, 1, lo_bound ? DIAG_A_LE : DIAG_A_GE, false);
   }
   p.A = B; p.lda = ldb; p.B = T; p.ldb = ldt; p.K = (int)n;
   if (lo_bound) p.khi_mode = KR_TILE_N; else p.klo_mode = KR_TILE_N;
-  if (!inplace_right) return gemm_launch(h, p, false, tr, 1);
-  p.tiles_m = (p.M + BM - 1) / BM; p.tiles_n = (p.N + BN - 1) / BN; p.ksplit = 1;
-  const int vec = (aligned16(p.A, p.lda) && aligned16(p.B, p.ldb)) ? 2 : 1;
-  const int grid = p.tiles_m;
-  if (tr) { if (vec == 2) dmma_trmm_right_inplace_kernel<true, 2><<<grid, NTHREADS, GEMM_SMEM_BYTES, h->stream>>>(p);
-            else dmma_trmm_right_inplace_kernel<true, 1><<<grid, NTHREADS, GEMM_SMEM_BYTES, h->stream>>>(p); }
-  else    { if (vec == 2) dmma_trmm_right_inplace_kernel<false, 2><<<grid, NTHREADS, GEMM_SMEM_BYTES, h->stream>>>(p);
-            else dmma_trmm_right_inplace_kernel<false, 1><<<grid, NTHREADS, GEMM_SMEM_BYTES, h->stream>>>(p); }
-  LAUNCH_CHECK(h);
-  return CAP_OK;
+  // tall panels: one CTA per 128-row block walking all column tiles (balanced, and the only safe order in place)
+  const bool rowpanel = inplace_right || (m + BM - 1) / BM >= 2 * (int64_t)h->num_sms;
+  return gemm_launch(h, p, false, tr, 1, lo_bound ? DIAG_B_LE : DIAG_B_GE, rowpanel);
 }
 
 int cap_dtrmm_oop(cap_handle_t h, char side, char uplo, char trans, char diag, int64_t m, int64_t n, double alpha,

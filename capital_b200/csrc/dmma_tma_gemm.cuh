@@ -1,0 +1,424 @@
+// Warp-specialised, persistent FP64 DMMA tile engine for sm_100a: TMA (cp.async.bulk.tensor) producer
+// warp + mbarrier ring + 8 consumer warps that do nothing but LDS.128 and DMMA.8x8x4.
+//
+// Same contractions as dmma_gemm.cuh (gemm / syrk / trmm / split-K Gram; reference
+// src/blas/interface.hpp:43-97), used whenever the operands satisfy TMA's alignment rules (16-byte
+// base, even leading dimension); the cp.async engine stays as the path for everything else.
+//
+// Why a second engine (profiles/r01_ncu_full_cpasync_engine.txt): in the cp.async kernel every warp
+// also computes bounds/addresses and meets the others at a CTA barrier once per 16 k-columns; the DMMA
+// pipe was active 80-84 % of the time.  Here
+//   * one elected producer lane issues the TMA boxes of a stage (out-of-range parts are zero-filled by
+//     the hardware, so there is no bounds arithmetic at all) and runs ahead across tiles;
+//   * consumers wait on a "full" mbarrier, read fragments, issue DMMAs, release the stage through an
+//     "empty" mbarrier -- no CTA-wide barrier anywhere in the main loop, the two warps that share an
+//     SM sub-partition drift out of phase and cover each other's fragment-load latency;
+//   * CTAs are persistent (grid = #SMs), so the epilogue of one tile overlaps the loads of the next;
+//   * tiles that touch the diagonal of a triangular operand or of a triangular C skip, at 16x16-block
+//     granularity, the DMMAs that would only multiply structural zeros / compute unwanted entries.
+//     Column pairs are dealt to warps as {wn, 7-wn} so that the skipped work is balanced over the four
+//     SM sub-partitions (each keeps 9/16 of a diagonal block's work).
+//
+// Shared-memory tiles use the TMA 128-byte swizzle (16-byte chunk index XOR (row & 7)):
+//   K-contiguous operand : one box  [128 mn][16 k]       row = 128 B
+//   MN-contiguous operand: 8 boxes  [16 k][16 mn] (2 KB) row = 128 B
+// and the fragment <-> row assignment below makes every LDS.128 phase hit 8 distinct chunks.
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "dmma_gemm.cuh"
+
+namespace capk {
+
+constexpr int T_STAGES = 6;
+constexpr int T_TILE_BYTES = 128 * 16 * 8;            // 16 KB per operand per stage
+constexpr int T_STAGE_BYTES = 2 * T_TILE_BYTES;       // 32 KB
+constexpr int T_CONSUMER_WARPS = 8;
+constexpr int T_THREADS = (T_CONSUMER_WARPS + 4) * 32;  // + one producer warpgroup (register budgets move in units of 4 warps)
+constexpr int T_REGS_CONSUMER = 232, T_REGS_PRODUCER = 40;
+constexpr int T_SMEM_BYTES = T_STAGES * T_STAGE_BYTES + 1024 /*alignment slack*/ + 256 /*mbarriers*/;
+
+enum : int { SCHED_RASTER = 0, SCHED_TRI = 1, SCHED_ROWPANEL_DESC = 2, SCHED_ROWPANEL_ASC = 3, SCHED_TM_DESC = 4 };
+// which operand is triangular on the diagonal k-block (the relation that holds for NON-zero entries)
+enum : int { DIAG_NONE = 0, DIAG_A_LE = 1 /* r <= k */, DIAG_A_GE = 2 /* r >= k */, DIAG_B_LE = 3 /* k <= c */, DIAG_B_GE = 4 /* k >= c */ };
+
+struct TmaGemmParams {
+  double* C; const double* Cin;
+  int64_t ldc, ldcin;
+  int M, N, K;
+  double alpha, beta;
+  int klo_mode, khi_mode;
+  int c_tri;
+  int diag;                 // DIAG_*: skip structural zeros of the triangular operand
+  int ksplit, k_per_split;
+  int64_t c_split_stride;
+  int tiles_m, tiles_n;
+  int sched;
+  int units, subs;          // persistent loop: unit = blockIdx.x + i*gridDim.x, `subs` tiles per unit
+  int c_vec2;               // C/Cin 16-byte aligned with even ld: paired-row stores allowed
+};
+
+// ------------------------------------------------------------------------------------------ PTX wrappers
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\n"
+      "bra WAIT_%=;\n"
+      "DONE_%=:\n"
+      "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar) {
+  asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+               ::"r"(smem_u32(smem_dst)), "l"(map), "r"(c0), "r"(c1), "r"(smem_u32(bar)) : "memory");
+}
+
+// ------------------------------------------------------------------------------------------ work decode
+// stage kt of a tile covers k0 = k_first + kt*k_step .. k0+15 (k_step = +-16: row-panel schedules walk k in
+// alternating directions so that a panel block is re-read while it is still in L2); the diagonal 128-block
+// of a triangular operand starts at k = diag_origin.
+struct TileInfo { int tm, tn, kz, k_first, k_step, nk, diag_origin; };
+
+__device__ __forceinline__ TileInfo decode_tile(const TmaGemmParams& p, int unit, int sub) {
+  TileInfo t;
+  int tile = unit;
+  t.kz = 0;
+  if (p.sched == SCHED_ROWPANEL_DESC) { t.tm = unit; t.tn = p.tiles_n - 1 - sub; }
+  else if (p.sched == SCHED_ROWPANEL_ASC) { t.tm = unit; t.tn = sub; }
+  else {
+    const int per_k = (p.sched == SCHED_TRI) ? p.tiles_m * (p.tiles_m + 1) / 2 : p.tiles_m * p.tiles_n;
+    if (p.ksplit > 1) { t.kz = unit / per_k; tile = unit - t.kz * per_k; }
+    if (p.sched == SCHED_TRI) {
+      int col = 0, rem = tile;
+      while (rem > col) { rem -= col + 1; ++col; }
+      t.tm = (p.c_tri == CTRI_UPPER) ? rem : col;
+      t.tn = (p.c_tri == CTRI_UPPER) ? col : rem;
+    } else if (p.sched == SCHED_TM_DESC) {   // longest-k tiles first when k grows with tm
+      t.tm = p.tiles_m - 1 - tile / p.tiles_n; t.tn = tile % p.tiles_n;
+    } else if (p.klo_mode == KR_TILE_M) {    // k shrinks with tm: plain tm-major order is already longest-first
+      t.tm = tile / p.tiles_n; t.tn = tile % p.tiles_n;
+    } else {
+      constexpr int GROUP = 8;
+      const int per_group = GROUP * p.tiles_n;
+      const int first_m = (tile / per_group) * GROUP;
+      const int gsize = min(p.tiles_m - first_m, GROUP);
+      t.tm = first_m + (tile % per_group) % gsize;
+      t.tn = (tile % per_group) / gsize;
+    }
+  }
+  const int m0 = t.tm * BM, n0 = t.tn * BN;
+  int k_begin = 0, k_end = p.K;
+  if (p.klo_mode == KR_TILE_M) k_begin = m0; else if (p.klo_mode == KR_TILE_N) k_begin = n0;
+  if (p.khi_mode == KR_TILE_M) k_end = min(p.K, m0 + BM); else if (p.khi_mode == KR_TILE_N) k_end = min(p.K, n0 + BN);
+  if (p.ksplit > 1) { k_begin = max(k_begin, t.kz * p.k_per_split); k_end = min(k_end, (t.kz + 1) * p.k_per_split); }
+  t.nk = k_end > k_begin ? (k_end - k_begin + BK - 1) / BK : 0;
+  const bool descending = (p.sched == SCHED_ROWPANEL_DESC || p.sched == SCHED_ROWPANEL_ASC) && (sub & 1);
+  t.k_step = descending ? -BK : BK;
+  t.k_first = descending ? k_begin + (t.nk - 1) * BK : k_begin;
+  t.diag_origin = (p.diag == DIAG_A_LE || p.diag == DIAG_A_GE) ? m0 : n0;
+  return t;
+}
+
+// skip tiles entirely outside the stored triangle of C (only reachable with the rectangular raster)
+__device__ __forceinline__ bool tile_outside_tri(const TmaGemmParams& p, const TileInfo& t) {
+  if (p.c_tri == CTRI_UPPER && t.tn * BN + BN - 1 < t.tm * BM) return true;
+  if (p.c_tri == CTRI_LOWER && t.tm * BM + BM - 1 < t.tn * BN) return true;
+  return false;
+}
+
+// ------------------------------------------------------------------------------------------ consumer side
+// Lane (g = lane>>2, t = lane&3).  pi(g) spreads the 8 DMMA rows of a K-contiguous tile over smem rows
+// whose (row & 7) differ in bit 2 between neighbouring g, which is what makes the swizzled LDS.128
+// conflict-free (lanes 0..7 of a phase are g in {2q, 2q+1} x t in 0..3).
+__device__ __forceinline__ int pi8(int g) { return ((g & 1) << 2) | (g >> 1); }
+
+// local row of accumulator row-tile i (0..7) for this lane's g
+template <bool A_KC>
+__device__ __forceinline__ int acc_row(int wm, int i, int g) {
+  return A_KC ? wm * 64 + 8 * i + pi8(g) : wm * 64 + 16 * (i >> 1) + 2 * g + (i & 1);
+}
+// local column of accumulator col-tile jj (0..3), C-fragment column index cidx (0..7)
+template <bool B_KC>
+__device__ __forceinline__ int acc_col(int wn, int jj, int cidx) {
+  const int pair = (jj < 2) ? wn : 7 - wn;
+  return B_KC ? 16 * pair + 8 * (jj & 1) + pi8(cidx) : 16 * pair + 2 * cidx + (jj & 1);
+}
+
+// 8-bit block mask, bit (j*2+q): row group j (16 rows: wm*64+16j..) x column pair q (16 cols: pair wn or 7-wn)
+__device__ __forceinline__ uint32_t diag_mask(int kind, int s, int wm, int wn) {
+  uint32_t m = 0;
+#pragma unroll
+  for (int j = 0; j < 4; ++j)
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
+      const int rg = 4 * wm + j, pr = q ? 7 - wn : wn;
+      bool need = true;
+      if (kind == DIAG_A_LE) need = rg <= s;
+      else if (kind == DIAG_A_GE) need = rg >= s;
+      else if (kind == DIAG_B_LE) need = s <= pr;
+      else if (kind == DIAG_B_GE) need = s >= pr;
+      m |= (need ? 1u : 0u) << (j * 2 + q);
+    }
+  return m;
+}
+__device__ __forceinline__ uint32_t ctri_mask(int c_tri, int wm, int wn) {
+  uint32_t m = 0;
+#pragma unroll
+  for (int j = 0; j < 4; ++j)
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
+      const int rg = 4 * wm + j, pr = q ? 7 - wn : wn;
+      const bool need = (c_tri == CTRI_UPPER) ? rg <= pr : rg >= pr;
+      m |= (need ? 1u : 0u) << (j * 2 + q);
+    }
+  return m;
+}
+
+// Per-thread fragment addressing, computed once per kernel: every LDS.128 of a stage is
+// [stage base + one of these + compile-time immediate], so the main loop carries no address arithmetic.
+//   K-contiguous A : row r = wm*64 + 8i + pi(g), chunk (4h+t)^pi(g)         -> a0 ^ (h*64) + i*1024
+//   MN-contiguous A: box 4wm+j, k-row 8h+2t+e, chunk g^(2t+e)                -> a_e + h*1024 + j*2048
+//   K-contiguous B : row 16*pair_q + 8y + pi(g), chunk (4h+t)^pi(g)          -> b_q ^ (h*64) + y*1024
+//   MN-contiguous B: box pair_q, k-row 8h+2t+e, chunk g^(2t+e)               -> b_{q,e} + h*1024
+struct FragAddr { uint32_t a[2]; uint32_t b[4]; };
+
+template <bool A_KC, bool B_KC>
+__device__ __forceinline__ FragAddr frag_addr(int wm, int wn, int g, int t) {
+  FragAddr f;
+  if (A_KC) { f.a[0] = (uint32_t)((wm * 64 + pi8(g)) * 128 + ((t ^ pi8(g)) << 4)); f.a[1] = f.a[0] ^ 64u; }
+  else {
+#pragma unroll
+    for (int e = 0; e < 2; ++e) f.a[e] = (uint32_t)(wm * 8192 + (2 * t + e) * 128 + ((g ^ (2 * t + e)) << 4));
+  }
+#pragma unroll
+  for (int q = 0; q < 2; ++q) {
+    const int pair = q ? 7 - wn : wn;
+    if (B_KC) { f.b[2 * q] = (uint32_t)(T_TILE_BYTES + (16 * pair + pi8(g)) * 128 + ((t ^ pi8(g)) << 4)); f.b[2 * q + 1] = f.b[2 * q] ^ 64u; }
+    else {
+#pragma unroll
+      for (int e = 0; e < 2; ++e) f.b[2 * q + e] = (uint32_t)(T_TILE_BYTES + pair * 2048 + (2 * t + e) * 128 + ((g ^ (2 * t + e)) << 4));
+    }
+  }
+  return f;
+}
+
+template <int IMM>
+__device__ __forceinline__ void lds128(double& x, double& y, uint32_t addr) {
+  asm volatile("ld.shared.v2.f64 {%0, %1}, [%2+%3];" : "=d"(x), "=d"(y) : "r"(addr), "n"(IMM));
+}
+
+// One stage = 16 k-columns.  sbase: shared-space address of the stage (A tile, then B tile at +16 KB).
+template <bool A_KC, bool B_KC>
+__device__ __forceinline__ void consume_stage(uint32_t sbase, const FragAddr& f, double (&acc)[8][4][2], uint32_t mask) {
+  uint32_t aa[2], bb[4];
+#pragma unroll
+  for (int x = 0; x < 2; ++x) aa[x] = sbase + f.a[x];
+#pragma unroll
+  for (int x = 0; x < 4; ++x) bb[x] = sbase + f.b[x];
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    double a[2][8], b[2][4];
+    if (A_KC) {   // a[0][i] = k 8h+2t, a[1][i] = k 8h+2t+1 of row tile i
+      lds128<0 * 1024>(a[0][0], a[1][0], aa[h]); lds128<1 * 1024>(a[0][1], a[1][1], aa[h]);
+      lds128<2 * 1024>(a[0][2], a[1][2], aa[h]); lds128<3 * 1024>(a[0][3], a[1][3], aa[h]);
+      lds128<4 * 1024>(a[0][4], a[1][4], aa[h]); lds128<5 * 1024>(a[0][5], a[1][5], aa[h]);
+      lds128<6 * 1024>(a[0][6], a[1][6], aa[h]); lds128<7 * 1024>(a[0][7], a[1][7], aa[h]);
+    } else {      // a[e][2j], a[e][2j+1] = rows 16j+2g, 16j+2g+1 at k 8h+2t+e
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        if (h == 0) {
+          lds128<0 * 2048>(a[e][0], a[e][1], aa[e]); lds128<1 * 2048>(a[e][2], a[e][3], aa[e]);
+          lds128<2 * 2048>(a[e][4], a[e][5], aa[e]); lds128<3 * 2048>(a[e][6], a[e][7], aa[e]);
+        } else {
+          lds128<1024 + 0 * 2048>(a[e][0], a[e][1], aa[e]); lds128<1024 + 1 * 2048>(a[e][2], a[e][3], aa[e]);
+          lds128<1024 + 2 * 2048>(a[e][4], a[e][5], aa[e]); lds128<1024 + 3 * 2048>(a[e][6], a[e][7], aa[e]);
+        }
+      }
+    }
+    if (B_KC) {   // b[0][2q+y], b[1][2q+y]: column tile y of pair q
+#pragma unroll
+      for (int q = 0; q < 2; ++q) {
+        lds128<0>(b[0][2 * q], b[1][2 * q], bb[2 * q + h]);
+        lds128<1024>(b[0][2 * q + 1], b[1][2 * q + 1], bb[2 * q + h]);
+      }
+    } else {      // b[e][2q], b[e][2q+1] = columns 16*pair+2g, +1 at k 8h+2t+e
+#pragma unroll
+      for (int q = 0; q < 2; ++q)
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          if (h == 0) lds128<0>(b[e][2 * q], b[e][2 * q + 1], bb[2 * q + e]);
+          else lds128<1024>(b[e][2 * q], b[e][2 * q + 1], bb[2 * q + e]);
+        }
+    }
+    if (mask == 0xFFu) {
+#pragma unroll
+      for (int e = 0; e < 2; ++e)
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+#pragma unroll
+          for (int jj = 0; jj < 4; ++jj) dmma884(acc[i][jj], a[e][i], b[e][jj]);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+#pragma unroll
+        for (int q = 0; q < 2; ++q)
+          if ((mask >> (j * 2 + q)) & 1u) {
+#pragma unroll
+            for (int e = 0; e < 2; ++e)
+#pragma unroll
+              for (int x = 0; x < 2; ++x)
+#pragma unroll
+                for (int y = 0; y < 2; ++y) dmma884(acc[2 * j + x][2 * q + y], a[e][2 * j + x], b[e][2 * q + y]);
+          }
+    }
+  }
+}
+
+template <bool A_KC, bool B_KC>
+__device__ __forceinline__ void store_tile(const TmaGemmParams& p, const TileInfo& ti, double (&acc)[8][4][2], int wm, int wn, int g, int t) {
+  double* C = p.C;
+  double alpha = p.alpha, beta = p.beta;
+  if (p.ksplit > 1) { C += (int64_t)ti.kz * p.c_split_stride; alpha = 1.0; beta = 0.0; }
+  const int m0 = ti.tm * BM, n0 = ti.tn * BN;
+  const bool full = (m0 + BM <= p.M) && (n0 + BN <= p.N) && (p.c_tri == CTRI_FULL || ti.tm != ti.tn);
+  if (!A_KC && p.c_vec2 && full) {
+    // row tiles 2j and 2j+1 hold rows 16j+2g and 16j+2g+1: one 16-byte store per pair
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int r = m0 + acc_row<false>(wm, 2 * j, g);
+#pragma unroll
+      for (int jj = 0; jj < 4; ++jj)
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          const int c = n0 + acc_col<B_KC>(wn, jj, 2 * t + e);
+          double2 v = make_double2(alpha * acc[2 * j][jj][e], alpha * acc[2 * j + 1][jj][e]);
+          if (beta != 0.0) {
+            const double2 o = *reinterpret_cast<const double2*>(p.Cin + r + (int64_t)c * p.ldcin);
+            v.x += beta * o.x; v.y += beta * o.y;
+          }
+          *reinterpret_cast<double2*>(C + r + (int64_t)c * p.ldc) = v;
+        }
+    }
+    return;
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int r = m0 + acc_row<A_KC>(wm, i, g);
+    if (r >= p.M) continue;
+#pragma unroll
+    for (int jj = 0; jj < 4; ++jj)
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        const int c = n0 + acc_col<B_KC>(wn, jj, 2 * t + e);
+        if (c >= p.N) continue;
+        if (p.c_tri == CTRI_UPPER && r > c) continue;
+        if (p.c_tri == CTRI_LOWER && r < c) continue;
+        double v = alpha * acc[i][jj][e];
+        if (beta != 0.0) v += beta * p.Cin[r + (int64_t)c * p.ldcin];
+        C[r + (int64_t)c * p.ldc] = v;
+      }
+  }
+}
+
+// ------------------------------------------------------------------------------------------ kernel
+// A_KC: op(A) is K-contiguous in global memory (transa = 'T'); B_KC: op(B) is K-contiguous (transb = 'N').
+// mapA / mapB: 2-D tensor maps, dim0 = the contiguous index.  Boxes: K-contiguous {16 k, 128 mn};
+// MN-contiguous {16 mn, 16 k} (issued 8 times per stage).
+template <bool A_KC, bool B_KC>
+__global__ void __launch_bounds__(T_THREADS, 1)
+dmma_tma_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB, const TmaGemmParams p) {
+  extern __shared__ unsigned char smem_raw[];
+  unsigned char* tiles = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(tiles + T_STAGES * T_STAGE_BYTES);
+  uint64_t* empty_bar = full_bar + T_STAGES;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int s = 0; s < T_STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], T_CONSUMER_WARPS); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  __syncthreads();
+
+  int stage = 0;
+  uint32_t phase = 0;
+
+  if (warp >= T_CONSUMER_WARPS) {
+    // ===================== producer: one lane feeds the ring, running ahead across tiles =====================
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(T_REGS_PRODUCER));
+    if (warp == T_CONSUMER_WARPS && lane == 0) {
+      for (int unit = blockIdx.x; unit < p.units; unit += gridDim.x)
+        for (int sub = 0; sub < p.subs; ++sub) {
+          const TileInfo ti = decode_tile(p, unit, sub);
+          if (tile_outside_tri(p, ti)) continue;
+          const int m0 = ti.tm * BM, n0 = ti.tn * BN;
+          for (int kt = 0; kt < ti.nk; ++kt) {
+            mbar_wait(&empty_bar[stage], phase ^ 1u);
+            mbar_expect_tx(&full_bar[stage], T_STAGE_BYTES);
+            unsigned char* sA = tiles + stage * T_STAGE_BYTES;
+            unsigned char* sB = sA + T_TILE_BYTES;
+            const int k0 = ti.k_first + kt * ti.k_step;
+            if (A_KC) tma_load_2d(sA, &mapA, k0, m0, &full_bar[stage]);
+            else {
+#pragma unroll
+              for (int b = 0; b < 8; ++b) tma_load_2d(sA + b * 2048, &mapA, m0 + 16 * b, k0, &full_bar[stage]);
+            }
+            if (B_KC) tma_load_2d(sB, &mapB, k0, n0, &full_bar[stage]);
+            else {
+#pragma unroll
+              for (int b = 0; b < 8; ++b) tma_load_2d(sB + b * 2048, &mapB, n0 + 16 * b, k0, &full_bar[stage]);
+            }
+            if (++stage == T_STAGES) { stage = 0; phase ^= 1u; }
+          }
+        }
+    }
+    return;
+  }
+
+  // ===================== consumers =====================
+  asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(T_REGS_CONSUMER));
+  const int wm = warp >> 2, wn = warp & 3, g = lane >> 2, t = lane & 3;
+  const FragAddr fa = frag_addr<A_KC, B_KC>(wm, wn, g, t);
+  const uint32_t tiles_u32 = smem_u32(tiles);
+  for (int unit = blockIdx.x; unit < p.units; unit += gridDim.x)
+    for (int sub = 0; sub < p.subs; ++sub) {
+      const TileInfo ti = decode_tile(p, unit, sub);
+      if (tile_outside_tri(p, ti)) continue;
+      double acc[8][4][2];
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int jj = 0; jj < 4; ++jj) acc[i][jj][0] = acc[i][jj][1] = 0.0;
+      const uint32_t tile_mask = (p.c_tri != CTRI_FULL && ti.tm == ti.tn) ? ctri_mask(p.c_tri, wm, wn) : 0xFFu;
+      for (int kt = 0; kt < ti.nk; ++kt) {
+        uint32_t mask = tile_mask;
+        if (p.diag != DIAG_NONE) {
+          const int ds = (ti.k_first + kt * ti.k_step - ti.diag_origin) / BK;   // 16-row step inside the diagonal block
+          if (ds >= 0 && ds < BM / BK && ti.k_first + kt * ti.k_step >= ti.diag_origin) mask &= diag_mask(p.diag, ds, wm, wn);
+        }
+        mbar_wait(&full_bar[stage], phase);
+        if (mask != 0u) consume_stage<A_KC, B_KC>(tiles_u32 + stage * T_STAGE_BYTES, fa, acc, mask);
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty_bar[stage]);
+        if (++stage == T_STAGES) { stage = 0; phase ^= 1u; }
+      }
+      store_tile<A_KC, B_KC>(p, ti, acc, wm, wn, g, t);
+    }
+}
+
+}  // namespace capk

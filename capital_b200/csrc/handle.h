@@ -17,6 +17,8 @@ struct cap_handle_s {
   cudaEvent_t ev_a = nullptr, ev_b = nullptr;
   int* info_dev = nullptr;
   long long launches = 0;
+  void* encode_tiled = nullptr;       // cuTensorMapEncodeTiled
+  int engine = 0;                     // 0 = auto (TMA engine when alignment allows), 1 = cp.async engine only
   cap_ws_slot ws[CAP_WS_SLOTS];
 };
 

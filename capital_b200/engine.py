@@ -52,6 +52,10 @@ class Engine:
         s = torch.cuda.current_stream(self.device).cuda_stream
         _lib.check(self.lib.cap_set_stream(self.h, C.c_void_p(s)), "cap_set_stream")
 
+    def set_engine(self, engine):
+        """0 = auto (TMA engine when alignment allows), 1 = cp.async engine only."""
+        _lib.check(self.lib.cap_set_engine(self.h, int(engine)), "cap_set_engine")
+
     def close(self):
         if self.h:
             self.lib.cap_destroy(self.h)

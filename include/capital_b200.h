@@ -36,6 +36,9 @@ const char* cap_last_error(void);
 int cap_get_info(cap_handle_t h, int* info);                 /* syncs; LAPACK info of potrf/trtri since last reset */
 int cap_reset_info(cap_handle_t h);
 long long cap_kernel_launches(cap_handle_t h);               /* number of kernels this handle has launched */
+/* tile engine selection: 0 = auto (TMA/mbarrier warp-specialised engine whenever operands are 16-byte aligned
+ * with even leading dimensions, cp.async engine otherwise), 1 = cp.async engine only (A/B testing) */
+int cap_set_engine(cap_handle_t h, int engine);
 
 /* ---- memory (matrix<>::_assemble / _destroy_, src/matrix/structure.hpp:4-24, matrix.hpp:158) -- */
 int cap_malloc(void** dptr, size_t bytes);
