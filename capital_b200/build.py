@@ -7,7 +7,9 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libcapital_b200.so")
 SOURCES = ["capi.cu", "comm.cu"]
-HEADERS = ["dmma_gemm.cuh", "aux_kernels.cuh", "handle.h", os.path.join("..", "..", "include", "capital_b200.h")]
+def _headers():
+    hs = [f for f in os.listdir(CSRC) if f.endswith((".cuh", ".h"))]
+    return hs + [os.path.join("..", "..", "include", "capital_b200.h")]
 
 
 def nccl_dirs():
@@ -22,7 +24,7 @@ def stale():
     if not os.path.exists(LIB):
         return True
     t = os.path.getmtime(LIB)
-    return any(os.path.getmtime(os.path.join(CSRC, f)) > t for f in SOURCES + HEADERS)
+    return any(os.path.getmtime(os.path.join(CSRC, f)) > t for f in SOURCES + _headers())
 
 
 def build(force=False, verbose=False):

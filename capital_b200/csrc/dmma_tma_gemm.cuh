@@ -37,7 +37,7 @@ constexpr int T_TILE_BYTES = 128 * 16 * 8;            // 16 KB per operand per s
 constexpr int T_STAGE_BYTES = 2 * T_TILE_BYTES;       // 32 KB
 constexpr int T_CONSUMER_WARPS = 8;
 constexpr int T_THREADS = (T_CONSUMER_WARPS + 4) * 32;  // + one producer warpgroup (register budgets move in units of 4 warps)
-constexpr int T_REGS_CONSUMER = 232, T_REGS_PRODUCER = 40;
+constexpr int T_REGS_CONSUMER = 240, T_REGS_PRODUCER = 24;
 constexpr int T_SMEM_BYTES = T_STAGES * T_STAGE_BYTES + 1024 /*alignment slack*/ + 256 /*mbarriers*/;
 
 enum : int { SCHED_RASTER = 0, SCHED_TRI = 1, SCHED_ROWPANEL_DESC = 2, SCHED_ROWPANEL_ASC = 3, SCHED_TM_DESC = 4 };
@@ -221,70 +221,86 @@ __device__ __forceinline__ void lds128(double& x, double& y, uint32_t addr) {
   asm volatile("ld.shared.v2.f64 {%0, %1}, [%2+%3];" : "=d"(x), "=d"(y) : "r"(addr), "n"(IMM));
 }
 
-// One stage = 16 k-columns.  sbase: shared-space address of the stage (A tile, then B tile at +16 KB).
-template <bool A_KC, bool B_KC>
-__device__ __forceinline__ void consume_stage(uint32_t sbase, const FragAddr& f, double (&acc)[8][4][2], uint32_t mask) {
-  uint32_t aa[2], bb[4];
+// Fragments of one half stage (8 k-columns = 2 DMMA k-steps e = 0, 1).
+struct Frags { double a[2][8]; double b[2][4]; };
+
+// sbase: shared-space address of the stage (A tile, then B tile at +16 KB); H: which half of its 16 k-columns.
+template <bool A_KC, bool B_KC, int H>
+__device__ __forceinline__ void load_frags(uint32_t sbase, const FragAddr& f, Frags& fr) {
+  if (A_KC) {   // a[0][i] = k 8h+2t, a[1][i] = k 8h+2t+1 of row tile i
+    const uint32_t aa = sbase + f.a[H];
+    lds128<0 * 1024>(fr.a[0][0], fr.a[1][0], aa); lds128<1 * 1024>(fr.a[0][1], fr.a[1][1], aa);
+    lds128<2 * 1024>(fr.a[0][2], fr.a[1][2], aa); lds128<3 * 1024>(fr.a[0][3], fr.a[1][3], aa);
+    lds128<4 * 1024>(fr.a[0][4], fr.a[1][4], aa); lds128<5 * 1024>(fr.a[0][5], fr.a[1][5], aa);
+    lds128<6 * 1024>(fr.a[0][6], fr.a[1][6], aa); lds128<7 * 1024>(fr.a[0][7], fr.a[1][7], aa);
+  } else {      // a[e][2j], a[e][2j+1] = rows 16j+2g, 16j+2g+1 at k 8h+2t+e
 #pragma unroll
-  for (int x = 0; x < 2; ++x) aa[x] = sbase + f.a[x];
-#pragma unroll
-  for (int x = 0; x < 4; ++x) bb[x] = sbase + f.b[x];
-#pragma unroll
-  for (int h = 0; h < 2; ++h) {
-    double a[2][8], b[2][4];
-    if (A_KC) {   // a[0][i] = k 8h+2t, a[1][i] = k 8h+2t+1 of row tile i
-      lds128<0 * 1024>(a[0][0], a[1][0], aa[h]); lds128<1 * 1024>(a[0][1], a[1][1], aa[h]);
-      lds128<2 * 1024>(a[0][2], a[1][2], aa[h]); lds128<3 * 1024>(a[0][3], a[1][3], aa[h]);
-      lds128<4 * 1024>(a[0][4], a[1][4], aa[h]); lds128<5 * 1024>(a[0][5], a[1][5], aa[h]);
-      lds128<6 * 1024>(a[0][6], a[1][6], aa[h]); lds128<7 * 1024>(a[0][7], a[1][7], aa[h]);
-    } else {      // a[e][2j], a[e][2j+1] = rows 16j+2g, 16j+2g+1 at k 8h+2t+e
-#pragma unroll
-      for (int e = 0; e < 2; ++e) {
-        if (h == 0) {
-          lds128<0 * 2048>(a[e][0], a[e][1], aa[e]); lds128<1 * 2048>(a[e][2], a[e][3], aa[e]);
-          lds128<2 * 2048>(a[e][4], a[e][5], aa[e]); lds128<3 * 2048>(a[e][6], a[e][7], aa[e]);
-        } else {
-          lds128<1024 + 0 * 2048>(a[e][0], a[e][1], aa[e]); lds128<1024 + 1 * 2048>(a[e][2], a[e][3], aa[e]);
-          lds128<1024 + 2 * 2048>(a[e][4], a[e][5], aa[e]); lds128<1024 + 3 * 2048>(a[e][6], a[e][7], aa[e]);
-        }
-      }
+    for (int e = 0; e < 2; ++e) {
+      const uint32_t aa = sbase + f.a[e];
+      lds128<H * 1024 + 0 * 2048>(fr.a[e][0], fr.a[e][1], aa); lds128<H * 1024 + 1 * 2048>(fr.a[e][2], fr.a[e][3], aa);
+      lds128<H * 1024 + 2 * 2048>(fr.a[e][4], fr.a[e][5], aa); lds128<H * 1024 + 3 * 2048>(fr.a[e][6], fr.a[e][7], aa);
     }
-    if (B_KC) {   // b[0][2q+y], b[1][2q+y]: column tile y of pair q
+  }
+  if (B_KC) {   // b[0][2q+y], b[1][2q+y]: column tile y of pair q
 #pragma unroll
-      for (int q = 0; q < 2; ++q) {
-        lds128<0>(b[0][2 * q], b[1][2 * q], bb[2 * q + h]);
-        lds128<1024>(b[0][2 * q + 1], b[1][2 * q + 1], bb[2 * q + h]);
-      }
-    } else {      // b[e][2q], b[e][2q+1] = columns 16*pair+2g, +1 at k 8h+2t+e
-#pragma unroll
-      for (int q = 0; q < 2; ++q)
-#pragma unroll
-        for (int e = 0; e < 2; ++e) {
-          if (h == 0) lds128<0>(b[e][2 * q], b[e][2 * q + 1], bb[2 * q + e]);
-          else lds128<1024>(b[e][2 * q], b[e][2 * q + 1], bb[2 * q + e]);
-        }
+    for (int q = 0; q < 2; ++q) {
+      const uint32_t bb = sbase + f.b[2 * q + H];
+      lds128<0>(fr.b[0][2 * q], fr.b[1][2 * q], bb);
+      lds128<1024>(fr.b[0][2 * q + 1], fr.b[1][2 * q + 1], bb);
     }
-    if (mask == 0xFFu) {
+  } else {      // b[e][2q], b[e][2q+1] = columns 16*pair+2g, +1 at k 8h+2t+e
 #pragma unroll
-      for (int e = 0; e < 2; ++e)
+    for (int q = 0; q < 2; ++q)
 #pragma unroll
-        for (int i = 0; i < 8; ++i)
+      for (int e = 0; e < 2; ++e) lds128<H * 1024>(fr.b[e][2 * q], fr.b[e][2 * q + 1], sbase + f.b[2 * q + e]);
+  }
+}
+
+// One k-step of a 16x16 block (2x2 DMMA tiles) behind a real, warp-uniform branch.  Written as a single
+// asm statement because the compiler otherwise predicates the four DMMAs, and a predicated-off DMMA
+// still costs its issue slot and the fixed spacing to the next one (profiles/r01_ncu_tma_engine.txt).
+__device__ __forceinline__ void dmma_block4(double (&c00)[2], double (&c01)[2], double (&c10)[2], double (&c11)[2],
+                                            double a0, double a1, double b0, double b1, uint32_t on) {
+  // (a loop that runs `on` = 0 or 1 times: ptxas if-converts a plain forward branch over four DMMAs back
+  //  into predication, but it cannot predicate a back edge)
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      ".reg .u32 cnt;\n"
+      "mov.u32 cnt, %12;\n"
+      "LOOP_%=:\n"
+      "setp.eq.u32 p, cnt, 0;\n"
+      "@p bra.uni SKIP_%=;\n"
+      "mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%8}, {%10}, {%0,%1};\n"
+      "mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%2,%3}, {%8}, {%11}, {%2,%3};\n"
+      "mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%4,%5}, {%9}, {%10}, {%4,%5};\n"
+      "mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%6,%7}, {%9}, {%11}, {%6,%7};\n"
+      "sub.u32 cnt, cnt, 1;\n"
+      "bra.uni LOOP_%=;\n"
+      "SKIP_%=:\n"
+      "}\n"
+      : "+d"(c00[0]), "+d"(c00[1]), "+d"(c01[0]), "+d"(c01[1]), "+d"(c10[0]), "+d"(c10[1]), "+d"(c11[0]), "+d"(c11[1])
+      : "d"(a0), "d"(a1), "d"(b0), "d"(b1), "r"(on));
+}
+
+__device__ __forceinline__ void mma_frags(double (&acc)[8][4][2], const Frags& fr, uint32_t mask) {
+  if (mask == 0xFFu) {
 #pragma unroll
-          for (int jj = 0; jj < 4; ++jj) dmma884(acc[i][jj], a[e][i], b[e][jj]);
-    } else {
+    for (int e = 0; e < 2; ++e)
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int jj = 0; jj < 4; ++jj) dmma884(acc[i][jj], fr.a[e][i], fr.b[e][jj]);
+  } else if (mask != 0u) {
+    // e outermost: the two updates of an accumulator are as far apart as the active blocks allow
+#pragma unroll
+    for (int e = 0; e < 2; ++e)
 #pragma unroll
       for (int j = 0; j < 4; ++j)
 #pragma unroll
         for (int q = 0; q < 2; ++q)
-          if ((mask >> (j * 2 + q)) & 1u) {
-#pragma unroll
-            for (int e = 0; e < 2; ++e)
-#pragma unroll
-              for (int x = 0; x < 2; ++x)
-#pragma unroll
-                for (int y = 0; y < 2; ++y) dmma884(acc[2 * j + x][2 * q + y], a[e][2 * j + x], b[e][2 * q + y]);
-          }
-    }
+          dmma_block4(acc[2 * j][2 * q], acc[2 * j][2 * q + 1], acc[2 * j + 1][2 * q], acc[2 * j + 1][2 * q + 1],
+                      fr.a[e][2 * j], fr.a[e][2 * j + 1], fr.b[e][2 * q], fr.b[e][2 * q + 1], (mask >> (j * 2 + q)) & 1u);
   }
 }
 
@@ -405,17 +421,31 @@ dmma_tma_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_cons
 #pragma unroll
         for (int jj = 0; jj < 4; ++jj) acc[i][jj][0] = acc[i][jj][1] = 0.0;
       const uint32_t tile_mask = (p.c_tri != CTRI_FULL && ti.tm == ti.tn) ? ctri_mask(p.c_tri, wm, wn) : 0xFFu;
+      // software pipeline: the fragments of the next half stage are in flight while the DMMAs of the
+      // current one issue (the 8 warps run in lockstep, so un-overlapped LDS bursts would idle the pipe)
+      Frags f0, f1;
+      if (ti.nk > 0) {
+        mbar_wait(&full_bar[stage], phase);
+        load_frags<A_KC, B_KC, 0>(tiles_u32 + stage * T_STAGE_BYTES, fa, f0);
+      }
       for (int kt = 0; kt < ti.nk; ++kt) {
         uint32_t mask = tile_mask;
         if (p.diag != DIAG_NONE) {
-          const int ds = (ti.k_first + kt * ti.k_step - ti.diag_origin) / BK;   // 16-row step inside the diagonal block
-          if (ds >= 0 && ds < BM / BK && ti.k_first + kt * ti.k_step >= ti.diag_origin) mask &= diag_mask(p.diag, ds, wm, wn);
+          const int k0 = ti.k_first + kt * ti.k_step;
+          const int ds = (k0 - ti.diag_origin) / BK;   // 16-row step inside the diagonal block
+          if (k0 >= ti.diag_origin && ds < BM / BK) mask &= diag_mask(p.diag, ds, wm, wn);
         }
-        mbar_wait(&full_bar[stage], phase);
-        if (mask != 0u) consume_stage<A_KC, B_KC>(tiles_u32 + stage * T_STAGE_BYTES, fa, acc, mask);
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&empty_bar[stage]);
+        load_frags<A_KC, B_KC, 1>(tiles_u32 + stage * T_STAGE_BYTES, fa, f1);
+        mma_frags(acc, f0, mask);
+        const int cur = stage;
         if (++stage == T_STAGES) { stage = 0; phase ^= 1u; }
+        if (kt + 1 < ti.nk) {
+          mbar_wait(&full_bar[stage], phase);
+          load_frags<A_KC, B_KC, 0>(tiles_u32 + stage * T_STAGE_BYTES, fa, f0);
+        }
+        mma_frags(acc, f1, mask);
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty_bar[cur]);
       }
       store_tile<A_KC, B_KC>(p, ti, acc, wm, wn, g, t);
     }
