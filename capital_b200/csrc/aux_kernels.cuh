@@ -1,7 +1,5 @@
-// Small-block Cholesky + triangular inverse (the recursion's base case) and the HBM-bound helper
-// kernels of the path (pack/unpack, copies, masks, axpby, generators).
-//   potrf + trtri base case   lapack::engine::_potrf/_trtri  (reference src/lapack/interface.hpp:31-58,
-//                             called together at cacqr.hpp:20-22 and cholinv/policy.h:199-201)
+// HBM-bound helper kernels of the path (pack/unpack, copies, masks, axpby, generators); the small-block
+// Cholesky + triangular inverse lives in potrf_base.cuh.
 //   pack/unpack/copy          serialize<S1,S2>::invoke        (src/matrix/serialize.hpp:12-150)
 //   mask                      util::remove_triangle           (src/util/util.hpp:267-293)
 //   axpby                     summa.hpp:33,153
@@ -10,80 +8,9 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include "potrf_base.cuh"
+
 namespace capk {
-
-constexpr int BASE_NB = 128;                 // largest block factored by one CTA
-constexpr int BASE_LD = BASE_NB + 1;
-constexpr int BASE_THREADS = 512;
-constexpr int BASE_SMEM_BYTES = (BASE_NB * BASE_LD + BASE_NB) * 8;
-
-// One CTA: R = chol(A) (upper, A = R^T R) and X = R^{-1} for an n x n block, n <= 128.
-// Shared buffer S: upper triangle holds A then R; the strict lower triangle holds X^T; xd = diag(X).
-// Reads only the upper triangle of A.  Writes R into the upper triangle of A (strict lower untouched,
-// like LAPACK) and X into the upper triangle of Rinv (strict lower zero-filled when zero_lower).
-// info (device int, may be null): first non-positive pivot, 1-based, offset by info_base; 0 = ok.
-__global__ void __launch_bounds__(BASE_THREADS, 1)
-potrf_trtri_base_kernel(double* A, int64_t lda, double* Rinv, int64_t ldri, int n, int* info, int info_base,
-                        int write_r, int zero_lower, int skip_potrf, int lower) {
-  // lower != 0: the block is lower triangular; it is read and written transposed, so the same
-  // upper-triangular code yields L = chol(A) (A = L L^T) and L^{-1}.
-  extern __shared__ __align__(16) double sh[];
-  double* S = sh;
-  double* xd = sh + BASE_NB * BASE_LD;
-  __shared__ int s_bad;
-  const int tid = threadIdx.x;
-  if (tid == 0) s_bad = 0;
-  for (int idx = tid; idx < n * n; idx += BASE_THREADS) {
-    const int r = idx % n, c = idx / n;
-    S[r * BASE_LD + c] = (r <= c) ? (lower ? A[c + (int64_t)r * lda] : A[r + (int64_t)c * lda]) : 0.0;
-  }
-  __syncthreads();
-  // right-looking Cholesky on the upper triangle
-  for (int j = 0; j < (skip_potrf ? 0 : n); ++j) {
-    const double d = S[j * BASE_LD + j];
-    if (!(d > 0.0)) { if (tid == 0 && s_bad == 0) s_bad = j + 1; }
-    const double rd = 1.0 / sqrt(d > 0.0 ? d : 1.0);
-    __syncthreads();
-    for (int c = j + tid; c < n; c += BASE_THREADS) S[j * BASE_LD + c] = (c == j) ? sqrt(d > 0.0 ? d : 1.0) : S[j * BASE_LD + c] * rd;
-    __syncthreads();
-    const int w = n - j - 1;
-    for (int idx = tid; idx < w * w; idx += BASE_THREADS) {
-      const int r = j + 1 + idx / w, c = j + 1 + idx % w;
-      if (r <= c) S[r * BASE_LD + c] -= S[j * BASE_LD + r] * S[j * BASE_LD + c];
-    }
-    __syncthreads();
-  }
-  if (write_r)
-    for (int idx = tid; idx < n * n; idx += BASE_THREADS) {
-      const int r = idx % n, c = idx / n;
-      if (r <= c) { if (lower) A[c + (int64_t)r * lda] = S[r * BASE_LD + c]; else A[r + (int64_t)c * lda] = S[r * BASE_LD + c]; }
-    }
-  // X = R^{-1}: back substitution on all columns at once; X(i,c), c>i lives at S[c][i], X(i,i) in xd.
-  // RHS starts as I: lower storage is already zero, the unit diagonal is implicit.
-  for (int i = n - 1; i >= 0; --i) {
-    const double rinv = 1.0 / S[i * BASE_LD + i];
-    __syncthreads();
-    if (tid == 0) xd[i] = rinv;                                   // (1 - 0) / R_ii
-    for (int c = i + 1 + tid; c < n; c += BASE_THREADS) S[c * BASE_LD + i] *= rinv;
-    __syncthreads();
-    // rows r < i: B(r, c) -= R(r,i) * X(i,c) for c >= i   (c == i: B(r,i) lives at S[i][r], r<i)
-    const int w = n - i;
-    for (int idx = tid; idx < i * w; idx += BASE_THREADS) {
-      const int r = idx / w, c = i + idx % w;
-      const double x = (c == i) ? rinv : S[c * BASE_LD + i];
-      S[c * BASE_LD + r] -= S[r * BASE_LD + i] * x;
-    }
-    __syncthreads();
-  }
-  for (int idx = tid; idx < n * n; idx += BASE_THREADS) {
-    const int r = idx % n, c = idx / n;
-    double* out = lower ? &Rinv[c + (int64_t)r * ldri] : &Rinv[r + (int64_t)c * ldri];
-    if (r < c) *out = S[c * BASE_LD + r];
-    else if (r == c) *out = xd[r];
-    else if (zero_lower) *out = 0.0;
-  }
-  if (tid == 0 && info && s_bad && *info == 0) *info = info_base + s_bad;
-}
 
 // ---------------------------------------------------------------- HBM-bound helpers (vectorised where layout allows)
 // dst(r,c) = src(r,c) over an m x n window, column-major; mode: 0 all, 1 upper (r<=c) only, 2 lower only,
