@@ -173,8 +173,10 @@ static bool tma_eligible(cap_handle_t h, const GemmParams& p) {
 // persistent CTA then gets the same number of units, and with the triangular enumeration the same mix of
 // diagonal and full tiles); otherwise one unit per SM.
 static int pick_ksplit(cap_handle_t h, int ntiles, int64_t K, bool persistent) {
-  if (ntiles * 2 > h->num_sms || K < 2048) return 1;
-  const int64_t max_by_k = std::max<int64_t>(1, K / 1024);
+  if (ntiles * 2 > h->num_sms || K < 128) return 1;
+  // long K: slabs of >= 1024 rows; short K (the small products inside cholinv / trtri, where one 128x128 tile
+  // would otherwise sit on a single SM for K/16 x 2 us): slabs down to 4 pipeline stages
+  const int64_t max_by_k = std::max<int64_t>(1, K >= 8192 ? K / 1024 : K / 64);
   if (persistent) {
     int a = ntiles, b = h->num_sms;
     while (b) { int tmp = a % b; a = b; b = tmp; }
@@ -322,13 +324,13 @@ static int trmm_impl(cap_handle_t h, char side, char uplo, char trans, char diag
   if (left) {
     p.A = T; p.lda = ldt; p.B = B; p.ldb = ldb; p.K = (int)m;
     if (lo_bound) p.klo_mode = KR_TILE_M; else p.khi_mode = KR_TILE_M;
-    return gemm_launch(h, p, tr, false, 1, lo_bound ? DIAG_A_LE : DIAG_A_GE, false);
+    return gemm_launch(h, p, tr, false, -1, lo_bound ? DIAG_A_LE : DIAG_A_GE, false);
   }
   p.A = B; p.lda = ldb; p.B = T; p.ldb = ldt; p.K = (int)n;
   if (lo_bound) p.khi_mode = KR_TILE_N; else p.klo_mode = KR_TILE_N;
   // tall panels: one CTA per 128-row block walking all column tiles (balanced, and the only safe order in place)
   const bool rowpanel = inplace_right || (m + BM - 1) / BM >= 2 * (int64_t)h->num_sms;
-  return gemm_launch(h, p, false, tr, 1, lo_bound ? DIAG_B_LE : DIAG_B_GE, rowpanel);
+  return gemm_launch(h, p, false, tr, rowpanel ? 1 : -1, lo_bound ? DIAG_B_LE : DIAG_B_GE, rowpanel);
 }
 
 int cap_dtrmm_oop(cap_handle_t h, char side, char uplo, char trans, char diag, int64_t m, int64_t n, double alpha,

@@ -44,6 +44,22 @@ __device__ __forceinline__ void pb_mma32(double (&acc)[4][4][2], FA a, FB b, int
       for (int j = 0; j < 4; ++j) dmma884(acc[i][j], af[i], bf[j]);
   }
 }
+// 16x16 quadrant: acc(16x16) += A(16xK) * B(Kx16); acc[i][j][e]: row 8i+g, col 8j+2t+e.
+template <class FA, class FB>
+__device__ __forceinline__ void pb_mma16(double (&acc)[2][2][2], FA a, FB b, int K, int g, int t) {
+#pragma unroll 8
+  for (int s = 0; s < K / 4; ++s) {
+    double af[2], bf[2];
+#pragma unroll
+    for (int i = 0; i < 2; ++i) af[i] = a(8 * i + g, 4 * s + t);
+#pragma unroll
+    for (int j = 0; j < 2; ++j) bf[j] = b(4 * s + t, 8 * j + g);
+#pragma unroll
+    for (int i = 0; i < 2; ++i)
+#pragma unroll
+      for (int j = 0; j < 2; ++j) dmma884(acc[i][j], af[i], bf[j]);
+  }
+}
 __device__ __forceinline__ void pb_zero(double (&acc)[4][4][2]) {
 #pragma unroll
   for (int i = 0; i < 4; ++i)
@@ -141,49 +157,68 @@ potrf_trtri_base_kernel(double* A, int64_t lda, double* Rinv, int64_t ldri, int 
       if (bad && lane == 0 && s_bad == 0) s_bad = b * PB + bad;
     }
     __syncthreads();
-    // ---- phase 2: row panel (j > b) and W_i (i < b)
-    const int n_panel = skip_potrf ? 0 : nb - 1 - b;
-    if (warp < n_panel) {
-      const int j = b + 1 + warp;
-      double acc[4][4][2]; pb_zero(acc);
-      double* Abj = S + (b * PB) * PB_SLD + j * PB;
-      pb_mma32(acc, [&](int r, int k) { return Xbb[k * PB_XLD + r]; }, [&](int k, int c) { return Abj[k * PB_SLD + c]; }, g, t);
-      __syncwarp();
-      pb_store(acc, [&](int r, int c, double v) { Abj[r * PB_SLD + c] = v; }, g, t);
-    } else if (warp < n_panel + b) {
-      const int i = warp - n_panel;
-      double acc[4][4][2]; pb_zero(acc);
-      for (int k = i; k < b; ++k) {
-        const double* Xik = XB + pb_xidx(i, k) * PB * PB_XLD;
-        const double* Rkb = S + (k * PB) * PB_SLD + b * PB;
-        pb_mma32(acc, [&](int r, int kk) { return Xik[r * PB_XLD + kk]; }, [&](int kk, int c) { return Rkb[kk * PB_SLD + c]; }, g, t);
-      }
-      double* Wi = XB + pb_xidx(i, b) * PB * PB_XLD;
-      pb_store(acc, [&](int r, int c, double v) { Wi[r * PB_XLD + c] = v; }, g, t);
-    }
-    __syncthreads();
-    // ---- phase 3: trailing update (b < i <= j) and X_ib = -W_i X_bb (i < b)
+    // ---- phases 2 and 3: 32x32 block products, each split into four 16x16 quadrants = one warp-item each.
+    // Results stay in registers until every warp has finished reading (several products are in place).
     const int rem = nb - 1 - b;
-    const int n_trail = skip_potrf ? 0 : rem * (rem + 1) / 2;
-    if (warp < n_trail) {
-      int jj = 0, ii = warp;
-      while (ii > jj) { ii -= jj + 1; ++jj; }        // enumerate ii <= jj
-      const int i = b + 1 + ii, j = b + 1 + jj;
-      double acc[4][4][2]; pb_zero(acc);
-      const double* Rbi = S + (b * PB) * PB_SLD + i * PB;
-      const double* Rbj = S + (b * PB) * PB_SLD + j * PB;
-      double* Aij = S + (i * PB) * PB_SLD + j * PB;
-      pb_mma32(acc, [&](int r, int k) { return Rbi[k * PB_SLD + r]; }, [&](int k, int c) { return Rbj[k * PB_SLD + c]; }, g, t);
-      pb_store(acc, [&](int r, int c, double v) { Aij[r * PB_SLD + c] -= v; }, g, t);
-    } else if (warp < n_trail + b) {
-      const int i = warp - n_trail;
-      double* Wi = XB + pb_xidx(i, b) * PB * PB_XLD;
-      double acc[4][4][2]; pb_zero(acc);
-      pb_mma32(acc, [&](int r, int k) { return Wi[r * PB_XLD + k]; }, [&](int k, int c) { return Xbb[k * PB_XLD + c]; }, g, t);
-      __syncwarp();
-      pb_store(acc, [&](int r, int c, double v) { Wi[r * PB_XLD + c] = -v; }, g, t);
+    for (int phase = 2; phase <= 3; ++phase) {
+      const int n_main = skip_potrf ? 0 : (phase == 2 ? rem : rem * (rem + 1) / 2);   // panel blocks / trailing blocks
+      const int n_items = (n_main + b) * 4;
+      double acc[3][2][2][2];
+#pragma unroll
+      for (int round = 0; round < 3; ++round) {
+        const int item = warp + 8 * round;
+#pragma unroll
+        for (int i = 0; i < 2; ++i)
+#pragma unroll
+          for (int j = 0; j < 2; ++j) acc[round][i][j][0] = acc[round][i][j][1] = 0.0;
+        if (item >= n_items) continue;
+        const int blk = item >> 2, r0 = ((item >> 1) & 1) * 16, c0 = (item & 1) * 16;
+        if (blk < n_main && phase == 2) {          // R_bj = X_bb^T A_bj
+          const double* Abj = S + (b * PB) * PB_SLD + (b + 1 + blk) * PB;
+          pb_mma16(acc[round], [&](int r, int k) { return Xbb[k * PB_XLD + r0 + r]; }, [&](int k, int c) { return Abj[k * PB_SLD + c0 + c]; }, PB, g, t);
+        } else if (blk < n_main) {                 // A_ij -= R_bi^T R_bj
+          int jj = 0, ii = blk;
+          while (ii > jj) { ii -= jj + 1; ++jj; }
+          const double* Rbi = S + (b * PB) * PB_SLD + (b + 1 + ii) * PB;
+          const double* Rbj = S + (b * PB) * PB_SLD + (b + 1 + jj) * PB;
+          pb_mma16(acc[round], [&](int r, int k) { return Rbi[k * PB_SLD + r0 + r]; }, [&](int k, int c) { return Rbj[k * PB_SLD + c0 + c]; }, PB, g, t);
+        } else if (phase == 2) {                   // W_i = sum_k X_ik R_kb
+          const int i = blk - n_main;
+          for (int k = i; k < b; ++k) {
+            const double* Xik = XB + pb_xidx(i, k) * PB * PB_XLD;
+            const double* Rkb = S + (k * PB) * PB_SLD + b * PB;
+            pb_mma16(acc[round], [&](int r, int kk) { return Xik[(r0 + r) * PB_XLD + kk]; }, [&](int kk, int c) { return Rkb[kk * PB_SLD + c0 + c]; }, PB, g, t);
+          }
+        } else {                                   // X_ib = -W_i X_bb
+          const double* Wi = XB + pb_xidx(blk - n_main, b) * PB * PB_XLD;
+          pb_mma16(acc[round], [&](int r, int k) { return Wi[(r0 + r) * PB_XLD + k]; }, [&](int k, int c) { return Xbb[k * PB_XLD + c0 + c]; }, PB, g, t);
+        }
+      }
+      __syncthreads();
+#pragma unroll
+      for (int round = 0; round < 3; ++round) {
+        const int item = warp + 8 * round;
+        if (item >= n_items) continue;
+        const int blk = item >> 2, r0 = ((item >> 1) & 1) * 16, c0 = (item & 1) * 16;
+        double* dst; int ld; double sign = 1.0; bool accumulate = false;
+        if (blk < n_main && phase == 2) { dst = S + (b * PB) * PB_SLD + (b + 1 + blk) * PB; ld = PB_SLD; }
+        else if (blk < n_main) {
+          int jj = 0, ii = blk;
+          while (ii > jj) { ii -= jj + 1; ++jj; }
+          dst = S + ((b + 1 + ii) * PB) * PB_SLD + (b + 1 + jj) * PB; ld = PB_SLD; sign = -1.0; accumulate = true;
+        } else { dst = XB + pb_xidx(blk - n_main, b) * PB * PB_XLD; ld = PB_XLD; sign = (phase == 2) ? 1.0 : -1.0; }
+#pragma unroll
+        for (int i = 0; i < 2; ++i)
+#pragma unroll
+          for (int j = 0; j < 2; ++j)
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+              double* q = dst + (r0 + 8 * i + g) * ld + c0 + 8 * j + 2 * t + e;
+              *q = accumulate ? *q + sign * acc[round][i][j][e] : sign * acc[round][i][j][e];
+            }
+      }
+      __syncthreads();
     }
-    __syncthreads();
   }
 
   // ---- results
