@@ -203,11 +203,11 @@ def ours_arm(args):
     peaks = json.load(open(FP64_PEAKS)) if os.path.exists(FP64_PEAKS) else {"dmma_tflops_sustained": 36.6, "source": "fallback constant"}
     peak = float(peaks["dmma_tflops_sustained"])
     kflops = float(m_loc) * n * n                  # algorithmic flops of one launch: triangular multiply / syrk of m_loc x n
-    roofline = {"bound": "tensor", "kernel": "dmma_gemm_kernel<NN> as Q=A*Rinv (cap_cqr_apply)", "achieved": kflops / ms_apply * 1e-9, "peak": peak,
+    roofline = {"bound": "tensor", "kernel": "dmma_tma_gemm_kernel<A_MC,B_KC> as Q=A*Rinv, row-panel schedule (cap_cqr_apply)", "achieved": kflops / ms_apply * 1e-9, "peak": peak,
                 "unit": "TFLOP/s", "frac": kflops / ms_apply * 1e-9 / peak, "traffic": None,
                 "peak_source": "measured DMMA.8x8x4 issue-rate microkernel, sustained (tools/dmma_peak.cu -> profiles/fp64_peak.json); MEASURED_PEAKS.json has no FP64 entry",
                 "ms_per_launch": ms_apply, "algorithmic_flops_per_launch": kflops,
-                "gram": {"kernel": "dmma_gemm_kernel<TN> split-K + splitk_reduce (cap_cqr_gram)", "achieved": kflops / ms_gram * 1e-9, "frac": kflops / ms_gram * 1e-9 / peak, "ms_per_launch": ms_gram},
+                "gram": {"kernel": "dmma_tma_gemm_kernel<A_KC,B_KC> split-K + splitk_reduce (cap_cqr_gram)", "achieved": kflops / ms_gram * 1e-9, "frac": kflops / ms_gram * 1e-9 / peak, "ms_per_launch": ms_gram},
                 "potrf_trtri_ms": ms_small}
     del X, G
 
