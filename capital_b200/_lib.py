@@ -33,6 +33,12 @@ _SIGS = {
     "cap_allreduce_sum": [_ptr, _ptr, _ptr, _i64], "cap_reduce_sum": [_ptr, _ptr, _ptr, _i64, _int],
     "cap_bcast": [_ptr, _ptr, _ptr, _i64, _int], "cap_allgather": [_ptr, _ptr, _ptr, _ptr, _i64],
     "cap_sendrecv": [_ptr, _ptr, _ptr, _ptr, _i64, _int],
+    "cap_grid_create": [_ptr, _int, C.POINTER(_ptr)], "cap_grid_destroy": [_ptr],
+    "cap_grid_info": [_ptr] + [C.POINTER(_int)] * 5, "cap_grid_transpose": [_ptr, _ptr, _ptr, _ptr, _i64],
+    "cap_summa_gemm": [_ptr, _ptr, _chr, _chr, _i64, _i64, _i64, _dbl, _ptr, _i64, _ptr, _i64, _dbl, _ptr, _i64],
+    "cap_summa_trmm": [_ptr, _ptr, _chr, _chr, _chr, _chr, _i64, _i64, _dbl, _ptr, _i64, _ptr, _i64],
+    "cap_summa_syrk": [_ptr, _ptr, _chr, _chr, _i64, _i64, _dbl, _ptr, _i64, _ptr, _i64, _dbl, _ptr, _i64],
+    "cap_cholinv_factor": [_ptr, _ptr, _i64, _ptr, _i64, _ptr, _i64, _int, _int, _i64],
     "cap_cacqr_factor_1d": [_ptr, _ptr, _i64, _i64, _ptr, _i64, _ptr, _i64, _ptr, _i64, _int],
     "cap_cacqr_factor_1d_host": [_ptr, _ptr, _i64, _i64, _ptr, _i64, _ptr, _i64, _ptr, _i64, _int],
 }

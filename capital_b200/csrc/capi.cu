@@ -304,7 +304,8 @@ __global__ void set_unit_diag_kernel(double* T, int64_t ld, int n) {
 
 // C = alpha*op(T)*B (left) or alpha*B*op(T) (right).  t_clean: the other triangle of T is already zero.
 static int trmm_impl(cap_handle_t h, char side, char uplo, char trans, char diag, int64_t m, int64_t n, double alpha,
-                     const double* T, int64_t ldt, const double* B, int64_t ldb, double* C, int64_t ldc, bool t_clean, bool inplace_right) {
+                     const double* T, int64_t ldt, const double* B, int64_t ldb, double* C, int64_t ldc, bool t_clean, bool inplace_right,
+                     double beta = 0.0) {
   if (m < 0 || n < 0 || m > INT32_MAX || n > INT32_MAX) return cap_fail(CAP_ERR_ARG, "cap_dtrmm", "bad dimension");
   if (m == 0 || n == 0) return CAP_OK;
   const bool left = is_l(side), upper = is_u(uplo), tr = is_t(trans), unit = is_u(diag);
@@ -319,7 +320,7 @@ static int trmm_impl(cap_handle_t h, char side, char uplo, char trans, char diag
     T = tc; ldt = nt;
   }
   GemmParams p{};
-  p.C = C; p.Cin = C; p.ldc = ldc; p.ldcin = ldc; p.M = (int)m; p.N = (int)n; p.alpha = alpha; p.beta = 0.0;
+  p.C = C; p.Cin = C; p.ldc = ldc; p.ldcin = ldc; p.M = (int)m; p.N = (int)n; p.alpha = alpha; p.beta = beta;
   const bool lo_bound = (upper != tr);  // left: Upper/NoTrans or Lower/Trans -> k >= i ; right: those -> k <= j
   if (left) {
     p.A = T; p.lda = ldt; p.B = B; p.ldb = ldb; p.K = (int)m;
@@ -550,3 +551,6 @@ int cap_cacqr_factor_1d_host(cap_handle_t h, cap_comm_t comm, int64_t m_loc, int
   CUDA_TRY(cudaStreamSynchronize(h->stream));
   return CAP_OK;
 }
+
+// ------------------------------------------------------------------------------------------ process-grid algorithms
+#include "grid_algs.cuh"

@@ -69,3 +69,49 @@ class Comm:
         if self.ptr:
             self.lib.cap_comm_destroy(self.ptr)
             self.ptr = C.c_void_p()
+
+
+def default_depth(world):
+    """Depth c of the c x d x d grid used for `world` GPUs: 1 -> 1x1x1, 2 -> 2x1x1 (replicated operands, k split),
+    4 -> 1x2x2 (2D SUMMA), 8 -> 2x2x2 (the reference's cube, topo::square needs P = c^3)."""
+    return {1: 1, 2: 2, 4: 1, 8: 2}[world]
+
+
+def grid_coords(rank, c, d):
+    """rank -> (x, y, z), layout 0 of topo::square (reference src/util/topology.h:80-82)."""
+    return (rank % (d * c)) // c, rank // (d * c), rank % c
+
+
+def cyclic_block(a, x, y, d):
+    """Local block of a global array under the element-cyclic deal (structure.hpp:74-98): rows y::d, columns x::d."""
+    return a[y::d, x::d]
+
+
+def assemble_cyclic(blocks, d):
+    """Inverse of cyclic_block: blocks[(x, y)] -> global array."""
+    r, c = blocks[(0, 0)].shape
+    out = blocks[(0, 0)].new_empty((r * d, c * d)) if hasattr(blocks[(0, 0)], "new_empty") else None
+    if out is None:
+        import numpy as np
+        out = np.empty((r * d, c * d), dtype=blocks[(0, 0)].dtype)
+    for (x, y), b in blocks.items():
+        out[y::d, x::d] = b
+    return out
+
+
+class Grid:
+    """topo::square over the library's NCCL communicator (cap_grid_t)."""
+
+    def __init__(self, engine, comm, c):
+        from . import _lib
+        self.lib = engine.lib
+        self.ptr = C.c_void_p()
+        _lib.check(self.lib.cap_grid_create(comm.ptr if comm else None, int(c), C.byref(self.ptr)), "cap_grid_create")
+        v = [C.c_int() for _ in range(5)]
+        self.lib.cap_grid_info(self.ptr, *[C.byref(t) for t in v])
+        self.c, self.d, self.x, self.y, self.z = [t.value for t in v]
+
+    def close(self):
+        if self.ptr:
+            self.lib.cap_grid_destroy(self.ptr)
+            self.ptr = C.c_void_p()

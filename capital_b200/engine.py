@@ -119,6 +119,28 @@ class Engine:
         _lib.check(self.lib.cap_cacqr_factor_1d_host(self.h, comm, m, n, A_host.data_ptr(), m, Q_host.data_ptr(), m,
                                                      R_host.data_ptr(), n, num_iter), "cap_cacqr_factor_1d_host")
 
+    # ---- process grid: summa / cholinv (all dimensions local) --------------------------------------
+    def summa_gemm(self, grid, A, B, Cm, m, n, k, transa="N", transb="N", alpha=1.0, beta=0.0):
+        _lib.check(self.lib.cap_summa_gemm(self.h, grid.ptr, _c(transa), _c(transb), m, n, k, alpha, A.data_ptr(), _ld(A),
+                                           B.data_ptr(), _ld(B), beta, Cm.data_ptr(), _ld(Cm)), "cap_summa_gemm")
+
+    def summa_trmm(self, grid, T, B, m, n, side="L", uplo="U", trans="N", diag="N", alpha=1.0):
+        _lib.check(self.lib.cap_summa_trmm(self.h, grid.ptr, _c(side), _c(uplo), _c(trans), _c(diag), m, n, alpha,
+                                           T.data_ptr(), _ld(T), B.data_ptr(), _ld(B)), "cap_summa_trmm")
+
+    def summa_syrk(self, grid, A, Cm, n, k, uplo="U", trans="T", alpha=1.0, beta=0.0, At=None):
+        _lib.check(self.lib.cap_summa_syrk(self.h, grid.ptr, _c(uplo), _c(trans), n, k, alpha, A.data_ptr(), _ld(A),
+                                           At.data_ptr() if At is not None else None, _ld(At) if At is not None else 0,
+                                           beta, Cm.data_ptr(), _ld(Cm)), "cap_summa_syrk")
+
+    def grid_transpose(self, grid, src, dst):
+        _lib.check(self.lib.cap_grid_transpose(self.h, grid.ptr, src.data_ptr(), dst.data_ptr(), src.numel()), "cap_grid_transpose")
+
+    def cholinv_factor(self, grid, A, Rinv, complete_inv=True, split=1, bc_global=2048):
+        n = A.shape[0]
+        _lib.check(self.lib.cap_cholinv_factor(self.h, grid.ptr, n, A.data_ptr(), _ld(A), Rinv.data_ptr(), _ld(Rinv),
+                                               int(bool(complete_inv)), int(split), int(bc_global)), "cap_cholinv_factor")
+
     # ---- serialize / generators -----------------------------------------------------------------
     def copy2d(self, dst, src, m, n, mode=0):
         _lib.check(self.lib.cap_copy2d(self.h, dst.data_ptr(), _ld(dst), src.data_ptr(), _ld(src), m, n, mode), "cap_copy2d")

@@ -101,6 +101,33 @@ int cap_bcast(cap_handle_t h, cap_comm_t comm, double* buf, int64_t count, int r
 int cap_allgather(cap_handle_t h, cap_comm_t comm, const double* send, double* recv, int64_t count_per_rank);
 int cap_sendrecv(cap_handle_t h, cap_comm_t comm, const double* send, double* recv, int64_t count, int peer);
 
+/* ---- process grid: topo::square (src/util/topology.h:67-143) and the algorithms that run on it ---------------
+ * c x d x d grid over `world` (size == c*d*d, d % c == 0 or d == 1), rank -> (x, y, z) as the reference's layout 0;
+ * row / column / depth / slice communicators are NCCL splits.  A global matrix is dealt element-cyclically over
+ * the d x d face (process (x,y) holds A[y + d*i, x + d*j]) and replicated over depth, as in src/matrix/structure.hpp:74-98.
+ * All dimensions below are LOCAL block dimensions; all calls are collective over the grid and stream-ordered. */
+typedef struct cap_grid_s* cap_grid_t;
+int cap_grid_create(cap_comm_t world, int c, cap_grid_t* grid);      /* world may be NULL for a single rank */
+int cap_grid_destroy(cap_grid_t grid);
+int cap_grid_info(cap_grid_t grid, int* c, int* d, int* x, int* y, int* z);
+/* util::transpose (src/util/util.hpp:233-247): dst <- the block of the process at (y, x) in the same layer */
+int cap_grid_transpose(cap_handle_t h, cap_grid_t grid, const double* src, double* dst, int64_t count);
+/* matmult::summa::invoke, gemm overload (src/alg/matmult/summa/summa.hpp:7-44) */
+int cap_summa_gemm(cap_handle_t h, cap_grid_t grid, char transa, char transb, int64_t m, int64_t n, int64_t k, double alpha,
+                   const double* A, int64_t lda, const double* B, int64_t ldb, double beta, double* C, int64_t ldc);
+/* trmm overload (summa.hpp:47-83): B <- alpha*op(T)*B or alpha*B*op(T), in place */
+int cap_summa_trmm(cap_handle_t h, cap_grid_t grid, char side, char uplo, char trans, char diag, int64_t m, int64_t n, double alpha,
+                   const double* T, int64_t ldt, double* B, int64_t ldb);
+/* syrk overloads (summa.hpp:86-161): C(uplo) <- alpha*A^T*A + beta*C ('T', A k x n) or alpha*A*A^T ('N', A n x k);
+ * At = grid-transposed copy of A if the caller has one (the 4-argument overload), else NULL */
+int cap_summa_syrk(cap_handle_t h, cap_grid_t grid, char uplo, char trans, int64_t n, int64_t k, double alpha,
+                   const double* A, int64_t lda, const double* At, int64_t ldat, double beta, double* C, int64_t ldc);
+/* cholesky::cholinv::factor (src/alg/cholesky/cholinv/cholinv.hpp:6-29): A (local n_loc x n_loc block of the SPD
+ * matrix) <- local part of R (upper), Rinv <- local part of R^-1; base case = ReplicateComp (policy.h:226-305) at
+ * global size <= bc_global; split as in cholinv.hpp:107 (1 = halves). */
+int cap_cholinv_factor(cap_handle_t h, cap_grid_t grid, int64_t n_loc, double* A, int64_t lda, double* Rinv, int64_t ldri,
+                       int complete_inv, int split, int64_t bc_global);
+
 /* ---- algorithm entry points (device-resident; src/alg/...) ----------------------------------- */
 /* qr::cacqr::factor, 1D (cacqr.hpp:219-248 -> invoke_1d :174-193).  A is the local m_loc x n row block
  * (untouched), Q the output block, R the n x n upper factor (full layout, strict lower zero).
