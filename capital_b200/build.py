@@ -40,6 +40,25 @@ def build(force=False, verbose=False):
     return LIB
 
 
+HOST_BIN = os.path.join(HERE, "host", "bin")
+HOST_MAINS = ["cacqr", "cholinv", "summa_gemm"]
+
+
+def build_host(force=False):
+    """C++ host drivers (argv-compatible with the reference's bench mains) linked against the C-ABI library."""
+    os.makedirs(HOST_BIN, exist_ok=True)
+    hdr = [os.path.join(HERE, "host", "capital.hpp"), os.path.join(HERE, "host", "bench", "common.hpp"), LIB]
+    for name in HOST_MAINS:
+        src, out = os.path.join(HERE, "host", "bench", name + ".cpp"), os.path.join(HOST_BIN, name)
+        if not force and os.path.exists(out) and all(os.path.getmtime(f) <= os.path.getmtime(out) for f in hdr + [src]):
+            continue
+        subprocess.run(["g++", "-O2", "-std=c++17", "-Wall", "-o", out, src, "-L" + HERE, "-l:libcapital_b200.so", "-lpthread",
+                        "-Wl,-rpath,$ORIGIN/../..", "-Wl,-rpath," + nccl_dirs()[1], "-Wl,-rpath,/usr/local/cuda/lib64",
+                        "-Wl,--allow-shlib-undefined"], check=True)
+    return HOST_BIN
+
+
 if __name__ == "__main__":
     import sys
     print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    print(build_host(force="--force" in sys.argv))

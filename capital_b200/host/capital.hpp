@@ -1,0 +1,423 @@
+// C++ host of capital-b200: the reference's engine / matrix / topology / algorithm entry points
+// (huttered40/capital, src/) re-stated over the C ABI of include/capital_b200.h, so that code written
+// against the reference -- e.g. its bench mains -- drives device-resident data on B200s.
+//
+//   blas::engine::_gemm/_trmm/_syrk      src/blas/interface.h:57-66, arg packs src/blas/engine.h:23-130
+//   lapack::engine::_potrf/_trtri        src/lapack/interface.h:49-53, arg packs src/lapack/engine.h:23-84
+//   matrix<T,U,Structure>                src/matrix/matrix.h:9-97 (local block of an element-cyclic matrix)
+//   topo::square / topo::rect            src/util/topology.h:16-143
+//   matmult::summa::invoke               src/alg/matmult/summa/summa.hpp:7-161
+//   cholesky::cholinv<>::factor          src/alg/cholesky/cholinv/cholinv.hpp:6-47
+//   qr::cacqr<>::factor                  src/alg/qr/cacqr/cacqr.hpp:219-270
+//
+// Differences that a device back end forces: all matrix storage is DEVICE memory;
+// triangular matrices are kept in full n x n storage with an explicit zero triangle (packed storage only
+// through pack()/unpack()); one process per GPU, ranks come from torchrun-style environment variables and
+// the NCCL id is exchanged through a file under /tmp (one node).  Header-only; link libcapital_b200.so.
+#pragma once
+#include <unistd.h>
+
+#include <cassert>
+#include <chrono>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <stdexcept>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "../../include/capital_b200.h"
+
+namespace capital {
+
+inline void check(int rc, const char* what) {
+  if (rc != CAP_OK) throw std::runtime_error(std::string(what) + ": " + cap_last_error());
+}
+
+// One process = one GPU.  RANK / WORLD_SIZE / LOCAL_RANK / MASTER_PORT as set by torch.distributed.run
+// (or any launcher that exports them); a single process needs nothing.
+class runtime {
+public:
+  static runtime& get() { static runtime r; return r; }
+  cap_handle_t handle() const { return h_; }
+  cap_comm_t world() const { return world_; }
+  int rank() const { return rank_; }
+  int size() const { return size_; }
+  void barrier() {   // stream drain + a 1-element allreduce: the role of PMPI_Barrier in the bench mains
+    if (size_ > 1) check(cap_allreduce_sum(h_, world_, token_, 1), "barrier");
+    check(cap_synchronize(h_), "cap_synchronize");
+  }
+  double max_over_ranks(double v) {   // PMPI_Allreduce(MAX) of a host scalar, through the device
+    if (size_ == 1) return v;
+    std::vector<double> all(size_, 0.0);
+    all[rank_] = v;
+    check(cap_h2d_async(h_, gather_, all.data(), sizeof(double) * size_), "h2d");
+    check(cap_allreduce_sum(h_, world_, gather_, size_), "allreduce");
+    check(cap_d2h_async(h_, all.data(), gather_, sizeof(double) * size_), "d2h");
+    check(cap_synchronize(h_), "sync");
+    double m = 0; for (double x : all) m = x > m ? x : m;
+    return m;
+  }
+  ~runtime() {
+    if (token_) cap_free(token_);
+    if (gather_) cap_free(gather_);
+    if (world_) cap_comm_destroy(world_);
+    if (h_) cap_destroy(h_);
+  }
+
+private:
+  runtime() {
+    auto env = [](const char* k, int dflt) { const char* v = getenv(k); return v ? atoi(v) : dflt; };
+    rank_ = env("RANK", 0); size_ = env("WORLD_SIZE", 1);
+    const int local = env("LOCAL_RANK", rank_);
+    check(cap_create(&h_, local), "cap_create");
+    check(cap_malloc((void**)&token_, 8), "cap_malloc");
+    check(cap_memset_async(h_, token_, 0, 8), "memset");
+    check(cap_malloc((void**)&gather_, 8 * (size_t)size_), "cap_malloc");
+    if (size_ > 1) {
+      char id[128];
+      const std::string path = "/tmp/capital_b200_ncclid_" + std::string(getenv("MASTER_PORT") ? getenv("MASTER_PORT") : "0") + "_" +
+                               std::string(getenv("TORCHELASTIC_RUN_ID") ? getenv("TORCHELASTIC_RUN_ID") : "run");
+      if (rank_ == 0) {
+        check(cap_comm_unique_id(id), "cap_comm_unique_id");
+        const std::string tmp = path + ".tmp";
+        FILE* f = fopen(tmp.c_str(), "wb");
+        if (!f || fwrite(id, 1, 128, f) != 128) throw std::runtime_error("cannot write " + tmp);
+        fclose(f);
+        rename(tmp.c_str(), path.c_str());
+      } else {
+        FILE* f = nullptr;
+        for (int tries = 0; tries < 6000 && !(f = fopen(path.c_str(), "rb")); ++tries) std::this_thread::sleep_for(std::chrono::milliseconds(10));
+        if (!f || fread(id, 1, 128, f) != 128) throw std::runtime_error("cannot read " + path);
+        fclose(f);
+      }
+      check(cap_comm_init_rank(&world_, id, size_, rank_), "cap_comm_init_rank");
+      barrier();
+      if (rank_ == 0) unlink(path.c_str());
+    }
+  }
+  cap_handle_t h_ = nullptr;
+  cap_comm_t world_ = nullptr;
+  double *token_ = nullptr, *gather_ = nullptr;
+  int rank_ = 0, size_ = 1;
+};
+
+inline cap_handle_t handle() { return runtime::get().handle(); }
+
+}  // namespace capital
+
+// ------------------------------------------------------------------------------------------ blas::engine
+namespace blas {
+enum class Order : unsigned char { AblasRowMajor = 0x0, AblasColumnMajor = 0x1 };
+enum class Transpose : unsigned char { AblasNoTrans = 0x0, AblasTrans = 0x1 };
+enum class Side : unsigned char { AblasLeft = 0x0, AblasRight = 0x1 };
+enum class UpLo : unsigned char { AblasLower = 0x0, AblasUpper = 0x1 };
+enum class Diag : unsigned char { AblasNonUnit = 0x0, AblasUnit = 0x1 };
+
+template <typename T> struct ArgPack_gemm {
+  ArgPack_gemm(Order o, Transpose ta, Transpose tb, T a, T b) : order(o), transposeA(ta), transposeB(tb), alpha(a), beta(b) {}
+  Order order; Transpose transposeA, transposeB; T alpha, beta;
+};
+template <typename T> struct ArgPack_trmm {
+  ArgPack_trmm(Order o, Side s, UpLo u, Transpose t, Diag d, T a) : order(o), side(s), uplo(u), transposeA(t), diag(d), alpha(a) {}
+  Order order; Side side; UpLo uplo; Transpose transposeA; Diag diag; T alpha;
+};
+template <typename T> struct ArgPack_syrk {
+  ArgPack_syrk(Order o, UpLo u, Transpose t, T a, T b) : order(o), uplo(u), transposeA(t), alpha(a), beta(b) {}
+  Order order; UpLo uplo; Transpose transposeA; T alpha, beta;
+};
+inline char chr(Transpose t) { return t == Transpose::AblasTrans ? 'T' : 'N'; }
+inline char chr(Side s) { return s == Side::AblasLeft ? 'L' : 'R'; }
+inline char chr(UpLo u) { return u == UpLo::AblasUpper ? 'U' : 'L'; }
+inline char chr(Diag d) { return d == Diag::AblasUnit ? 'U' : 'N'; }
+
+// Same argument order as the reference's static engine; pointers are device pointers.  Only the column-major
+// double case exists on the path (the reference specialises for double only, interface.hpp:43,62,82).
+class engine {
+public:
+  static void _gemm(double* A, double* B, double* C, int64_t m, int64_t n, int64_t k, int64_t lda, int64_t ldb, int64_t ldc,
+                    const ArgPack_gemm<double>& p) {
+    assert(p.order == Order::AblasColumnMajor);
+    capital::check(cap_dgemm(capital::handle(), chr(p.transposeA), chr(p.transposeB), m, n, k, p.alpha, A, lda, B, ldb, p.beta, C, ldc), "cap_dgemm");
+  }
+  static void _trmm(double* A, double* B, int64_t m, int64_t n, int64_t lda, int64_t ldb, const ArgPack_trmm<double>& p) {
+    assert(p.order == Order::AblasColumnMajor);
+    capital::check(cap_dtrmm(capital::handle(), chr(p.side), chr(p.uplo), chr(p.transposeA), chr(p.diag), m, n, p.alpha, A, lda, B, ldb), "cap_dtrmm");
+  }
+  static void _syrk(double* A, double* C, int64_t n, int64_t k, int64_t lda, int64_t ldc, const ArgPack_syrk<double>& p) {
+    assert(p.order == Order::AblasColumnMajor);
+    capital::check(cap_dsyrk(capital::handle(), chr(p.uplo), chr(p.transposeA), n, k, p.alpha, A, lda, p.beta, C, ldc), "cap_dsyrk");
+  }
+};
+}  // namespace blas
+
+// ------------------------------------------------------------------------------------------ lapack::engine
+namespace lapack {
+enum class Order : unsigned char { AlapackRowMajor = 0x0, AlapackColumnMajor = 0x1 };
+enum class UpLo : unsigned char { AlapackLower = 0x0, AlapackUpper = 0x1 };
+enum class Diag : unsigned char { AlapackNonUnit = 0x0, AlapackUnit = 0x1 };
+struct ArgPack_potrf { ArgPack_potrf(Order o, UpLo u) : order(o), uplo(u) {} Order order; UpLo uplo; };
+struct ArgPack_trtri { ArgPack_trtri(Order o, UpLo u, Diag d) : order(o), uplo(u), diag(d) {} Order order; UpLo uplo; Diag diag; };
+class engine {
+public:
+  // LAPACK `info` stays on the device (cap_get_info); the reference discards it (lapack/interface.hpp:39,54)
+  static void _potrf(double* A, int n, int lda, const ArgPack_potrf& p) {
+    assert(p.order == Order::AlapackColumnMajor);
+    capital::check(cap_dpotrf(capital::handle(), p.uplo == UpLo::AlapackUpper ? 'U' : 'L', n, A, lda), "cap_dpotrf");
+  }
+  static void _trtri(double* A, int n, int lda, const ArgPack_trtri& p) {
+    assert(p.order == Order::AlapackColumnMajor);
+    capital::check(cap_dtrtri(capital::handle(), p.uplo == UpLo::AlapackUpper ? 'U' : 'L', p.diag == Diag::AlapackUnit ? 'U' : 'N', n, A, lda), "cap_dtrtri");
+  }
+};
+}  // namespace lapack
+
+// ------------------------------------------------------------------------------------------ topology
+namespace topo {
+// c x d x d grid (topology.h:67-143, layout 0); P = c*d*d with d % c == 0 or d == 1
+class square {
+public:
+  explicit square(size_t c_, size_t layout_ = 0, size_t num_chunks_ = 0) : layout(layout_), num_chunks(num_chunks_) {
+    auto& rt = capital::runtime::get();
+    rank = rt.rank(); size = rt.size();
+    capital::check(cap_grid_create(rt.world(), (int)c_, &grid), "cap_grid_create");
+    int ci, di, xi, yi, zi;
+    cap_grid_info(grid, &ci, &di, &xi, &yi, &zi);
+    c = ci; d = di; x = xi; y = yi; z = zi;
+  }
+  ~square() { cap_grid_destroy(grid); }
+  square(const square&) = delete;
+  cap_grid_t grid = nullptr;
+  int rank, size;
+  size_t c, d, x, y, z, layout, num_chunks;
+};
+// Tall-skinny grid of the CholeskyQR path (topology.h:16-65).  Only the 1D case c == 1 (d = P) is on the
+// graded path (cacqr.hpp:229); the tunable c x d x c grid is SURVEY 8(f) "next".
+class rect {
+public:
+  explicit rect(size_t c_, size_t layout_ = 0, size_t num_chunks_ = 0) : layout(layout_), num_chunks(num_chunks_) {
+    auto& rt = capital::runtime::get();
+    rank = rt.rank(); size = rt.size();
+    if (c_ != 1) throw std::runtime_error("topo::rect: only the 1D grid (c == 1) is implemented");
+    c = 1; d = size; x = 0; y = rank; z = 0;
+  }
+  int rank, size;
+  size_t c, d, x, y, z, layout, num_chunks;
+};
+}  // namespace topo
+
+// ------------------------------------------------------------------------------------------ matrix
+struct rect {};
+struct uppertri {};
+struct lowertri {};
+
+// Local block of an element-cyclic distributed matrix (matrix.h:9-97) in DEVICE memory, column-major,
+// leading dimension = local rows.  X = columns, Y = rows, as everywhere in the reference.  Triangular
+// structures keep full storage (zeros in the other triangle); num_elems() is the full local count.
+template <typename ScalarT = double, typename DimensionT = int64_t, typename StructurePolicy = rect>
+class matrix {
+  static_assert(sizeof(ScalarT) == sizeof(double), "FP64 only: the reference specialises its engines for double only");
+public:
+  using ScalarType = ScalarT; using DimensionType = DimensionT; using StructureType = StructurePolicy;
+  matrix() = default;
+  matrix(DimensionT globalDimensionX, DimensionT globalDimensionY, int64_t globalPgridX, int64_t globalPgridY) {
+    _register_(globalDimensionX, globalDimensionY, globalPgridX, globalPgridY);
+  }
+  // injection constructor (matrix.hpp:53-74): wrap a caller-owned device pointer
+  matrix(ScalarT* data, DimensionT dimensionX, DimensionT dimensionY, DimensionT globalPgridX, DimensionT globalPgridY)
+      : data_(data), owned_(false), dimX_(dimensionX), dimY_(dimensionY), gX_(dimensionX * globalPgridX), gY_(dimensionY * globalPgridY) {}
+  matrix(const matrix& rhs) { copy_from(rhs); }
+  matrix(matrix&& rhs) noexcept { steal(rhs); }
+  matrix& operator=(const matrix& rhs) { if (this != &rhs) { _destroy_(); copy_from(rhs); } return *this; }
+  matrix& operator=(matrix&& rhs) noexcept { if (this != &rhs) { _destroy_(); steal(rhs); } return *this; }
+  ~matrix() { _destroy_(); }
+
+  void _register_(DimensionT globalDimensionX, DimensionT globalDimensionY, int64_t globalPgridX, int64_t globalPgridY) {
+    _destroy_();
+    gX_ = globalDimensionX; gY_ = globalDimensionY;
+    dimX_ = (globalDimensionX + globalPgridX - 1) / globalPgridX;     // ceil: zero padding past the edge (matrix.hpp:8-11)
+    dimY_ = (globalDimensionY + globalPgridY - 1) / globalPgridY;
+    capital::check(cap_malloc((void**)&data_, sizeof(double) * (size_t)dimX_ * dimY_), "cap_malloc");
+    capital::check(cap_memset_async(capital::handle(), data_, 0, sizeof(double) * (size_t)dimX_ * dimY_), "cap_memset_async");
+    owned_ = true;
+  }
+  void _destroy_() { if (owned_ && data_) cap_free(data_); data_ = nullptr; owned_ = false; }
+
+  ScalarT* data() const { return data_; }
+  DimensionT num_elems() const { return dimX_ * dimY_; }
+  DimensionT num_rows_local() const { return dimY_; }
+  DimensionT num_columns_local() const { return dimX_; }
+  DimensionT num_rows_global() const { return gY_; }
+  DimensionT num_columns_global() const { return gX_; }
+
+  // structure.hpp:106-129: element t of the local block (column by column) = t-th drand48 value after srand48(key)
+  void distribute_random(int64_t, int64_t, int64_t, int64_t, int64_t key) {
+    capital::check(cap_fill_random(capital::handle(), data_, dimY_, dimY_, dimX_, key), "cap_fill_random");
+  }
+  // structure.hpp:69-103: a(gy,gx) seeded by max + N*min, + N on the diagonal when diagonallyDominant
+  void distribute_symmetric(int64_t localPgridX, int64_t localPgridY, int64_t globalPgridX, int64_t globalPgridY, int64_t, bool diagonallyDominant) {
+    capital::check(cap_fill_symmetric(capital::handle(), data_, dimY_, dimY_, dimX_, localPgridX, localPgridY, globalPgridX, globalPgridY,
+                                      gY_, diagonallyDominant ? 1 : 0), "cap_fill_symmetric");
+  }
+  std::vector<double> to_host() const {
+    std::vector<double> out((size_t)dimX_ * dimY_);
+    capital::check(cap_d2h_async(capital::handle(), out.data(), data_, sizeof(double) * out.size()), "cap_d2h_async");
+    capital::check(cap_synchronize(capital::handle()), "cap_synchronize");
+    return out;
+  }
+
+private:
+  void copy_from(const matrix& rhs) {
+    dimX_ = rhs.dimX_; dimY_ = rhs.dimY_; gX_ = rhs.gX_; gY_ = rhs.gY_; owned_ = false; data_ = nullptr;
+    if (!rhs.data_) return;
+    capital::check(cap_malloc((void**)&data_, sizeof(double) * (size_t)dimX_ * dimY_), "cap_malloc");
+    owned_ = true;
+    capital::check(cap_copy2d(capital::handle(), data_, dimY_, rhs.data_, dimY_, dimY_, dimX_, 0), "cap_copy2d");
+  }
+  void steal(matrix& rhs) {
+    data_ = rhs.data_; owned_ = rhs.owned_; dimX_ = rhs.dimX_; dimY_ = rhs.dimY_; gX_ = rhs.gX_; gY_ = rhs.gY_;
+    rhs.data_ = nullptr; rhs.owned_ = false;
+  }
+  ScalarT* data_ = nullptr;
+  bool owned_ = false;
+  DimensionT dimX_ = 0, dimY_ = 0, gX_ = 0, gY_ = 0;
+};
+
+// ------------------------------------------------------------------------------------------ matmult::summa
+namespace matmult {
+class summa {
+public:
+  // gemm (summa.hpp:7-44)
+  template <typename MA, typename MB, typename MC, typename CommType>
+  static void invoke(MA& A, MB& B, MC& C, CommType&& ci, blas::ArgPack_gemm<double>& p) {
+    const bool ta = p.transposeA == blas::Transpose::AblasTrans, tb = p.transposeB == blas::Transpose::AblasTrans;
+    const int64_t m = ta ? A.num_columns_local() : A.num_rows_local(), n = tb ? B.num_rows_local() : B.num_columns_local();
+    const int64_t k = ta ? A.num_rows_local() : A.num_columns_local();
+    capital::check(cap_summa_gemm(capital::handle(), ci.grid, blas::chr(p.transposeA), blas::chr(p.transposeB), m, n, k, p.alpha,
+                                  A.data(), A.num_rows_local(), B.data(), B.num_rows_local(), p.beta, C.data(), C.num_rows_local()), "cap_summa_gemm");
+  }
+  // trmm (summa.hpp:47-83): A triangular, B rectangular and overwritten
+  template <typename MA, typename MB, typename CommType>
+  static void invoke(MA& A, MB& B, CommType&& ci, blas::ArgPack_trmm<double>& p) {
+    capital::check(cap_summa_trmm(capital::handle(), ci.grid, blas::chr(p.side), blas::chr(p.uplo), blas::chr(p.transposeA), blas::chr(p.diag),
+                                  B.num_rows_local(), B.num_columns_local(), p.alpha, A.data(), A.num_rows_local(), B.data(), B.num_rows_local()), "cap_summa_trmm");
+  }
+  // syrk (summa.hpp:86-96): the grid-transposed copy is made inside
+  template <typename MS, typename MD, typename CommType>
+  static void invoke(MS& A, MD& C, CommType&& ci, blas::ArgPack_syrk<double>& p) {
+    const bool tr = p.transposeA == blas::Transpose::AblasTrans;
+    capital::check(cap_summa_syrk(capital::handle(), ci.grid, blas::chr(p.uplo), blas::chr(p.transposeA), C.num_columns_local(),
+                                  tr ? A.num_rows_local() : A.num_columns_local(), p.alpha, A.data(), A.num_rows_local(), nullptr, 0, p.beta,
+                                  C.data(), C.num_rows_local()), "cap_summa_syrk");
+  }
+};
+}  // namespace matmult
+
+// ------------------------------------------------------------------------------------------ cholesky::cholinv
+namespace cholesky {
+namespace policy { namespace cholinv {
+// Policy tags of the reference (cholinv/policy.h).  Storage and buffering choices are the library's here;
+// every base-case tag maps to the replicated base case (ReplicateComp, policy.h:226-305) -- the reference's
+// NoReplication variants return wrong factors on d > 1 grids (header).
+struct Serialize { using structure = uppertri; }; struct NoSerialize { using structure = rect; };
+struct SaveIntermediates {}; struct FlushIntermediates {};
+struct ReplicateCommComp {}; struct ReplicateComp {}; struct NoReplication {}; struct NoReplicationOverlap {};
+}}  // namespace policy::cholinv
+
+template <class SerializePolicy = policy::cholinv::Serialize, class IntermediatesPolicy = policy::cholinv::SaveIntermediates,
+          class BaseCasePolicy = policy::cholinv::ReplicateComp>
+class cholinv {
+public:
+  template <typename ScalarT, typename DimensionT>
+  class info {
+  public:
+    using ScalarType = ScalarT; using DimensionType = DimensionT;
+    using alg_type = cholinv<SerializePolicy, IntermediatesPolicy, BaseCasePolicy>;
+    info(bool complete_inv_, DimensionT split_, int64_t bc_mult_dim_, char dir_) : complete_inv(complete_inv_), split(split_), bc_mult_dim(bc_mult_dim_), dir(dir_) {}
+    bool complete_inv; DimensionT split; int64_t bc_mult_dim; char dir;
+    matrix<ScalarT, DimensionT, uppertri> R, Rinv;      // full local storage, zeros outside the triangle
+    int lapack_info = 0;
+  };
+
+  // cholinv.hpp:6-29.  Base-case size follows cholinv.hpp:15-18: bcDimLocal = c*d scaled by 2^-bc_mult_dim
+  // (negative bc_mult_dim = smaller base case), clamped to [1, l]; recursion stops at global size d*l/bcDimLocal.
+  template <typename MatrixType, typename ArgType, typename CommType>
+  static void factor(const MatrixType& A, ArgType& args, CommType&& ci) {
+    assert(args.split > 0); assert(args.dir == 'U');
+    const int64_t l = A.num_rows_local();
+    int64_t bc = (int64_t)(ci.c * ci.d), mult = args.bc_mult_dim;
+    if (mult < 0) { for (int64_t i = 0; i < -mult; ++i) bc *= 2; } else { for (int64_t i = 0; i < mult; ++i) bc /= 2; }
+    bc = bc < 1 ? 1 : bc; bc = bc > l ? l : bc;
+    const int64_t bc_global = (int64_t)ci.d * (l / bc);
+    args.R = matrix<double, typename ArgType::DimensionType, uppertri>(A.num_columns_global(), A.num_rows_global(), ci.d, ci.d);
+    args.Rinv = matrix<double, typename ArgType::DimensionType, uppertri>(A.num_columns_global(), A.num_rows_global(), ci.d, ci.d);
+    capital::check(cap_copy2d(capital::handle(), args.R.data(), l, A.data(), l, l, l, 0), "cap_copy2d");
+    capital::check(cap_reset_info(capital::handle()), "cap_reset_info");
+    capital::check(cap_cholinv_factor(capital::handle(), ci.grid, l, args.R.data(), l, args.Rinv.data(), l, args.complete_inv ? 1 : 0,
+                                      (int)args.split, bc_global), "cap_cholinv_factor");
+  }
+  template <typename ArgType, typename CommType>
+  static matrix<double, typename ArgType::DimensionType, rect> construct_R(ArgType& args, CommType&&) { return to_rect(args.R); }
+  template <typename ArgType, typename CommType>
+  static matrix<double, typename ArgType::DimensionType, rect> construct_Rinv(ArgType& args, CommType&&) { return to_rect(args.Rinv); }
+
+private:
+  template <typename M>
+  static matrix<double, typename M::DimensionType, rect> to_rect(const M& src) {
+    matrix<double, typename M::DimensionType, rect> out(src.num_columns_local(), src.num_rows_local(), 1, 1);
+    capital::check(cap_copy2d(capital::handle(), out.data(), src.num_rows_local(), src.data(), src.num_rows_local(), src.num_rows_local(),
+                              src.num_columns_local(), 0), "cap_copy2d");
+    return out;
+  }
+};
+}  // namespace cholesky
+
+// ------------------------------------------------------------------------------------------ qr::cacqr
+namespace qr {
+namespace policy { namespace cacqr {
+struct Serialize { using structure = uppertri; }; struct NoSerialize { using structure = rect; };   // packed vs full Gram allreduce (policy.h:9-85)
+struct SaveIntermediates {}; struct FlushIntermediates {};
+}}  // namespace policy::cacqr
+
+template <class SerializePolicy = policy::cacqr::Serialize, class IntermediatesPolicy = policy::cacqr::SaveIntermediates>
+class cacqr {
+public:
+  template <typename ScalarT, typename DimensionT, typename CholeskyInversionType>
+  class info {
+  public:
+    using ScalarType = ScalarT; using DimensionType = DimensionT;
+    using alg_type = cacqr<SerializePolicy, IntermediatesPolicy>;
+    using cholesky_inverse_type = CholeskyInversionType;
+    template <typename CholeskyInversionArgType>
+    info(size_t num_iter_, CholeskyInversionArgType&& ci_args) : num_iter(num_iter_), cholesky_inverse_args(ci_args) {}
+    const size_t num_iter;                                   // 1 = CholeskyQR, 2 = CholeskyQR2
+    typename CholeskyInversionType::template info<ScalarT, DimensionT> cholesky_inverse_args;
+    matrix<ScalarT, DimensionT, rect> Q;
+    matrix<ScalarT, DimensionT, uppertri> R;                 // n x n, full storage
+  };
+
+  // cacqr.hpp:219-248 -> invoke_1d (:174-193) on the 1D grid; A is untouched, Q and R are (re)allocated on first use
+  template <typename MatrixType, typename ArgType, typename CommType>
+  static void factor(const MatrixType& A, ArgType& args, CommType&& ci) {
+    if (ci.c != 1) throw std::runtime_error("qr::cacqr::factor: only the 1D grid (c == 1) is implemented");
+    const int64_t m = A.num_rows_local(), n = A.num_columns_local();
+    if (!args.Q.data() || args.Q.num_rows_local() != m || args.Q.num_columns_local() != n)
+      args.Q = matrix<double, typename ArgType::DimensionType, rect>(A.num_columns_global(), A.num_rows_global(), ci.c, ci.d);
+    if (!args.R.data() || args.R.num_rows_local() != n)
+      args.R = matrix<double, typename ArgType::DimensionType, uppertri>(n, n, 1, 1);
+    auto& rt = capital::runtime::get();
+    capital::check(cap_cacqr_factor_1d(rt.handle(), rt.world(), m, n, A.data(), m, args.Q.data(), m, args.R.data(), n, (int)args.num_iter), "cap_cacqr_factor_1d");
+  }
+  template <typename ArgType, typename CommType>
+  static matrix<double, typename ArgType::DimensionType, rect> construct_Q(ArgType& args, CommType&&) { return args.Q; }
+  template <typename ArgType, typename CommType>
+  static matrix<double, typename ArgType::DimensionType, rect> construct_R(ArgType& args, CommType&&) {
+    matrix<double, typename ArgType::DimensionType, rect> out(args.R.num_columns_local(), args.R.num_rows_local(), 1, 1);
+    capital::check(cap_copy2d(capital::handle(), out.data(), args.R.num_rows_local(), args.R.data(), args.R.num_rows_local(),
+                              args.R.num_rows_local(), args.R.num_columns_local(), 0), "cap_copy2d");
+    return out;
+  }
+};
+}  // namespace qr
