@@ -1,0 +1,100 @@
+"""GPU: process-grid algorithms (SUMMA gemm/trmm/syrk, distributed cholinv) through the C ABI against numpy on the
+assembled global matrices (tools/grid_check.py), at every world size the box offers; the C++ host drivers; and
+the two tile engines against each other."""
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from conftest import ROOT, TOL_FACTOR, relerr
+
+pytestmark = pytest.mark.gpu
+
+
+def _run_grid_check(world, n, port):
+    script = os.path.join(ROOT, "tools", "grid_check.py")
+    if world == 1:
+        cmd = [sys.executable, script, str(n)]
+    else:
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=%d" % world, "--master-addr", "127.0.0.1",
+               "--master-port", str(port), script, str(n)]
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
+    assert out.returncode == 0 and "GRID CHECK PASSED" in out.stdout, out.stdout[-3000:] + out.stderr[-3000:]
+
+
+@pytest.mark.parametrize("world,n", [(1, 640), (2, 1024), (4, 1024), (8, 2048)])
+def test_grid_algorithms(world, n):
+    import torch
+    if torch.cuda.device_count() < world:
+        pytest.skip("needs %d GPUs" % world)
+    _run_grid_check(world, n, 29540 + world)
+
+
+def test_cpp_host_drivers():
+    """The reference's bench command lines (bench/qr/cacqr.cpp:14-25, bench/cholesky/cholinv.cpp:15-22,
+    bench/matmult/summa_gemm.cpp:19-25) run against the C++ host mirror."""
+    bindir = os.path.join(ROOT, "capital_b200", "host", "bin")
+    if not os.path.exists(os.path.join(bindir, "cacqr")):
+        pytest.skip("host drivers not built (python -m capital_b200.build)")
+    for cmd in (["cacqr", "2", "65536", "256", "1", "1", "1", "1", "0", "0", "0", "0", "1"],
+                ["cholinv", "2048", "1", "1", "1", "0", "0", "0", "1"],
+                ["summa_gemm", "1024", "768", "512", "1", "0", "0", "1"]):
+        out = subprocess.run([os.path.join(bindir, cmd[0])] + cmd[1:], capture_output=True, text=True, timeout=300)
+        assert out.returncode == 0 and "TFLOP/s" in out.stdout, out.stdout[-2000:] + out.stderr[-2000:]
+
+
+@pytest.mark.parametrize("side,uplo,tr", [(s, u, t) for s in "LR" for u in "UL" for t in "NT"])
+def test_trmm_diag_skipping_both_engines(engine, side, uplo, tr):
+    """Sizes that cross several 128-tiles with ragged edges: the TMA engine skips structural zeros of the
+    diagonal blocks, the cp.async engine multiplies them; both must agree with numpy."""
+    import torch
+    from capital_b200.engine import colmajor, to_colmajor
+    rng = np.random.default_rng(11)
+    m, n = (520, 300) if side == "L" else (300, 520)
+    nt = m if side == "L" else n
+    T = rng.random((nt, nt)); B = rng.random((m, n))
+    Tt = np.triu(T) if uplo == "U" else np.tril(T)
+    op = Tt.T if tr == "T" else Tt
+    ref = 1.25 * (op @ B if side == "L" else B @ op)
+    for eng_id in (0, 1):
+        engine.set_engine(eng_id)
+        t, b, c = to_colmajor(T), to_colmajor(B), colmajor(m, n)
+        engine.trmm_oop(t, b, c, m, n, side, uplo, tr, "N", 1.25); torch.cuda.synchronize()
+        assert relerr(c.cpu().numpy(), ref) <= TOL_FACTOR, (eng_id, side, uplo, tr)
+        engine._trmm(t, b, m, n, side, uplo, tr, "N", 1.25); torch.cuda.synchronize()
+        assert relerr(b.cpu().numpy(), ref) <= TOL_FACTOR, ("in place", eng_id, side, uplo, tr)
+    engine.set_engine(0)
+
+
+@pytest.mark.parametrize("uplo,tr", [("U", "T"), ("L", "T"), ("U", "N"), ("L", "N")])
+def test_syrk_masked_diagonal_tiles(engine, uplo, tr):
+    import torch
+    from capital_b200.engine import to_colmajor
+    rng = np.random.default_rng(12)
+    n, k = 650, 3000
+    A = rng.random((k, n)) if tr == "T" else rng.random((n, k))
+    C0 = rng.random((n, n))
+    full = 0.5 * (A.T @ A if tr == "T" else A @ A.T) + 2.0 * C0
+    ref = np.where(np.triu(np.ones((n, n))) > 0 if uplo == "U" else np.tril(np.ones((n, n))) > 0, full, C0)
+    for eng_id in (0, 1):
+        engine.set_engine(eng_id)
+        a, c = to_colmajor(A), to_colmajor(C0)
+        engine._syrk(a, c, n, k, uplo, tr, 0.5, 2.0); torch.cuda.synchronize()
+        assert relerr(c.cpu().numpy(), ref) <= TOL_FACTOR, (eng_id, uplo, tr)
+    engine.set_engine(0)
+
+
+def test_unaligned_operands_take_the_cpasync_engine(engine):
+    """Odd leading dimensions / 8-byte-aligned bases are outside TMA's rules: same results through the fallback."""
+    import torch
+    rng = np.random.default_rng(13)
+    m, n, k = 257, 131, 390
+    big_a = torch.as_tensor(rng.random((k + 3, m + 1)), device="cuda").t()   # column-major (m+1) x (k+3), ld = m+1 (even or odd)
+    big_b = torch.as_tensor(rng.random((n + 2, k + 1)), device="cuda").t()
+    A = big_a[1:m + 1, 1:k + 1]; B = big_b[1:k + 1, :n]                       # bases offset by one double
+    from capital_b200.engine import colmajor
+    C = colmajor(m, n)
+    engine._gemm(A, B, C, m, n, k, "N", "N", 1.0, 0.0); torch.cuda.synchronize()
+    assert relerr(C.cpu().numpy(), A.cpu().numpy() @ B.cpu().numpy()) <= TOL_FACTOR
