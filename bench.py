@@ -203,8 +203,15 @@ def ours_arm(args):
     peaks = json.load(open(FP64_PEAKS)) if os.path.exists(FP64_PEAKS) else {"dmma_tflops_sustained": 36.6, "source": "fallback constant"}
     peak = float(peaks["dmma_tflops_sustained"])
     kflops = float(m_loc) * n * n                  # algorithmic flops of one launch: triangular multiply / syrk of m_loc x n
+    traffic, traffic_src = None, None
+    tpath = os.path.join(ROOT, "profiles", "r01_traffic.json")
+    if os.path.exists(tpath):
+        tj = json.load(open(tpath))
+        traffic = float(tj["dram_bytes_per_element"]) * m_loc * n     # measured DRAM bytes per panel element x elements of this launch
+        traffic_src = tj["source"]
     roofline = {"bound": "tensor", "kernel": "dmma_tma_gemm_kernel<A_MC,B_KC> as Q=A*Rinv, row-panel schedule (cap_cqr_apply)", "achieved": kflops / ms_apply * 1e-9, "peak": peak,
-                "unit": "TFLOP/s", "frac": kflops / ms_apply * 1e-9 / peak, "traffic": None,
+                "unit": "TFLOP/s", "frac": kflops / ms_apply * 1e-9 / peak, "traffic": traffic, "traffic_unit": "bytes per launch (dram read + write)",
+                "traffic_source": traffic_src, "algorithmic_bytes_per_launch": 16.0 * m_loc * n,
                 "peak_source": "measured DMMA.8x8x4 issue-rate microkernel, sustained (tools/dmma_peak.cu -> profiles/fp64_peak.json); MEASURED_PEAKS.json has no FP64 entry",
                 "ms_per_launch": ms_apply, "algorithmic_flops_per_launch": kflops,
                 "gram": {"kernel": "dmma_tma_gemm_kernel<A_KC,B_KC> split-K + splitk_reduce (cap_cqr_gram)", "achieved": kflops / ms_gram * 1e-9, "frac": kflops / ms_gram * 1e-9 / peak, "ms_per_launch": ms_gram},

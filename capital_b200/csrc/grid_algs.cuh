@@ -259,6 +259,16 @@ __global__ void mask_cyclic_upper_kernel(double* __restrict__ A, int64_t lda, in
     if (y + (int64_t)d * r > x + (int64_t)d * c) A[r + (int64_t)c * lda] = 0.0;
 }
 
+// Optional phase profile of the distributed recursion (CAPITAL_B200_PROFILE=1): synchronises around every phase and
+// accumulates wall time per category; printed by rank 0 at the end of cap_cholinv_factor.  Off by default.
+struct PhaseProf {
+  bool on = false; double t[8] = {0, 0, 0, 0, 0, 0, 0, 0}; const char* names[8] = {"base", "trsm", "syrk", "inv", "copy", "transpose", "", ""};
+  std::chrono::steady_clock::time_point t0;
+  void begin(cap_handle_t h) { if (on) { cudaStreamSynchronize(h->stream); t0 = std::chrono::steady_clock::now(); } }
+  void end(cap_handle_t h, int cat) { if (on) { cudaStreamSynchronize(h->stream); t[cat] += std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count(); } }
+};
+static PhaseProf g_prof;
+
 struct CholinvCtx {
   cap_handle_t h; cap_grid_t g;
   double* A; int64_t lda; double* X; int64_t ldx;
@@ -302,7 +312,12 @@ static int cholinv_grid_base(const CholinvCtx& cx, int off, int len) {
 static int cholinv_grid_rec(const CholinvCtx& cx, int off, int len, bool top) {
   cap_handle_t h = cx.h; cap_grid_t g = cx.g;
   const int l1 = len >> cx.split;
-  if ((int64_t)len * g->d <= cx.bc_global || l1 < cx.split || l1 < 1) return cholinv_grid_base(cx, off, len);   // cholinv.hpp:93
+  if ((int64_t)len * g->d <= cx.bc_global || l1 < cx.split || l1 < 1) {   // cholinv.hpp:93
+    g_prof.begin(h);
+    const int rc = cholinv_grid_base(cx, off, len);
+    g_prof.end(h, 0);
+    return rc;
+  }
   const int l2 = len - l1;
   double* A12 = cx.A + off + (int64_t)(off + l1) * cx.lda;
   double* A22 = A12 + l1;
@@ -316,14 +331,23 @@ static int cholinv_grid_rec(const CholinvCtx& cx, int off, int len, bool top) {
   T1t = T1 + (int64_t)l1 * l1;
   CAP_TRY(cap_workspace(h, CAP_WS_CI_W, (size_t)2 * l1 * l2 * sizeof(double), &W));
   Wt = W + (int64_t)l1 * l2;
+  g_prof.begin(h);
   CAP_TRY(copy2d(h, T1, l1, X11, cx.ldx, l1, l1, 0));
+  g_prof.end(h, 4); g_prof.begin(h);
   CAP_TRY(cap_grid_transpose(h, g, T1, T1t, (int64_t)l1 * l1));
+  g_prof.end(h, 5); g_prof.begin(h);
   CAP_TRY(copy2d(h, W, l1, A12, cx.lda, l1, l2, 0));
+  g_prof.end(h, 4); g_prof.begin(h);
   CAP_TRY(summa_trmm_impl(h, g, 'L', 'U', 'T', 'N', l1, l2, 1.0, T1t, l1, W, l1, true));
+  g_prof.end(h, 1); g_prof.begin(h);
   CAP_TRY(copy2d(h, A12, cx.lda, W, l1, l1, l2, 0));
+  g_prof.end(h, 4);
   // trailing matrix update (cholinv.hpp:129-134): A22 -= R12^T R12, upper triangle of the local block only
+  g_prof.begin(h);
   CAP_TRY(cap_grid_transpose(h, g, W, Wt, (int64_t)l1 * l2));
+  g_prof.end(h, 5); g_prof.begin(h);
   CAP_TRY(cap_summa_syrk(h, g, 'U', 'T', l2, l1, -1.0, W, l1, Wt, l1, 1.0, A22, cx.lda));
+  g_prof.end(h, 2);
   CAP_TRY(cholinv_grid_rec(cx, off + l1, l2, false));
   if (!(top && !cx.complete_inv)) {
     // inverse completion (cholinv.hpp:147-156): Rinv12 = -(Rinv11 R12) Rinv22
@@ -332,12 +356,18 @@ static int cholinv_grid_rec(const CholinvCtx& cx, int off, int len, bool top) {
     CAP_TRY(cap_workspace(h, CAP_WS_CI_T1, (size_t)2 * l1 * l1 * sizeof(double), &T1));
     CAP_TRY(cap_workspace(h, CAP_WS_CI_W, (size_t)2 * l1 * l2 * sizeof(double), &W));
     CAP_TRY(cap_workspace(h, CAP_WS_CI_T2, (size_t)l2 * l2 * sizeof(double), &T2));
+    g_prof.begin(h);
     CAP_TRY(copy2d(h, T1, l1, X11, cx.ldx, l1, l1, 0));
     CAP_TRY(copy2d(h, W, l1, A12, cx.lda, l1, l2, 0));
+    g_prof.end(h, 4); g_prof.begin(h);
     CAP_TRY(summa_trmm_impl(h, g, 'L', 'U', 'N', 'N', l1, l2, 1.0, T1, l1, W, l1, true));
+    g_prof.end(h, 3); g_prof.begin(h);
     CAP_TRY(copy2d(h, T2, l2, X22, cx.ldx, l2, l2, 0));
+    g_prof.end(h, 4); g_prof.begin(h);
     CAP_TRY(summa_trmm_impl(h, g, 'R', 'U', 'N', 'N', l1, l2, -1.0, T2, l2, W, l1, true));
+    g_prof.end(h, 3); g_prof.begin(h);
     CAP_TRY(copy2d(h, X12, cx.ldx, W, l1, l1, l2, 0));
+    g_prof.end(h, 4);
   }
   return CAP_OK;
 }
@@ -351,7 +381,14 @@ int cap_cholinv_factor(cap_handle_t h, cap_grid_t g, int64_t n_loc, double* A, i
   if (n_loc <= 0 || n_loc * g->d > INT32_MAX || split < 1) return cap_fail(CAP_ERR_ARG, "cap_cholinv_factor", "bad argument");
   CAP_TRY(memset2d(h, Rinv, ldri, n_loc, n_loc));
   CholinvCtx cx{h, g, A, lda, Rinv, ldri, complete_inv, split, bc_global};
+  g_prof.on = getenv("CAPITAL_B200_PROFILE") != nullptr;
+  for (double& v : g_prof.t) v = 0;
   CAP_TRY(cholinv_grid_rec(cx, 0, (int)n_loc, true));
+  if (g_prof.on && g->rank == 0) {
+    fprintf(stderr, "[capital_b200 profile] cholinv n_loc=%lld grid %dx%dx%d:", (long long)n_loc, g->c, g->d, g->d);
+    for (int i = 0; i < 6; ++i) fprintf(stderr, " %s %.2f ms", g_prof.names[i], g_prof.t[i] * 1e3);
+    fprintf(stderr, "\n");
+  }
   // the strictly-lower local part of A still holds input values: R is upper (remove_triangle, util.hpp:267-293)
   dim3 gl((unsigned)((n_loc + 255) / 256), (unsigned)n_loc);
   mask_cyclic_upper_kernel<<<gl, 256, 0, h->stream>>>(A, lda, (int)n_loc, g->d, g->x, g->y);
