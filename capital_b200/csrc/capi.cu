@@ -265,6 +265,12 @@ static int gemm_launch(cap_handle_t h, GemmParams p, bool ta, bool tb, int want_
   return CAP_OK;
 }
 
+int cap_set_host_chunk_bytes(cap_handle_t h, size_t bytes) {
+  if (bytes < 4096) return cap_fail(CAP_ERR_ARG, "cap_set_host_chunk_bytes", "chunk too small");
+  h->host_chunk_bytes = bytes;
+  return CAP_OK;
+}
+
 int cap_set_engine(cap_handle_t h, int engine) {
   if (engine != 0 && engine != 1) return cap_fail(CAP_ERR_ARG, "cap_set_engine", "0 = auto, 1 = cp.async engine only");
   h->engine = engine;
@@ -538,19 +544,68 @@ int cap_cacqr_factor_1d(cap_handle_t h, cap_comm_t comm, int64_t m_loc, int64_t 
   return trmm_impl(h, 'R', 'U', 'N', 'N', n, n, 1.0, G1, n, G2, n, R, ldr, true, false);
 }
 
+// End to end from HOST memory, pipelined over row chunks on two streams:
+//   sweep 1: H2D of chunk i+1 (copy stream) overlaps the Gram of chunk i (G1 += A_i^T A_i);
+//   sweep 2: the in-place apply of chunk i overlaps the D2H of chunk i-1.
+// The step is PCIe-bound (2 x 8 m n bytes); what stays exposed is apply 1 + Gram 2 + the two small factorizations.
 int cap_cacqr_factor_1d_host(cap_handle_t h, cap_comm_t comm, int64_t m_loc, int64_t n, const double* A_host, int64_t lda,
                              double* Q_host, int64_t ldq, double* R_host, int64_t ldr, int num_iter) {
   if (lda != m_loc || ldq != m_loc || ldr != n) return cap_fail(CAP_ERR_ARG, "cap_cacqr_factor_1d_host", "host buffers must be dense (ld == rows)");
+  if (m_loc < 0 || n <= 0 || n > INT32_MAX || m_loc > INT32_MAX) return cap_fail(CAP_ERR_ARG, "cap_cacqr_factor_1d_host", "bad dimension");
+  if (num_iter < 1 || num_iter > 2) return cap_fail(CAP_ERR_ARG, "cap_cacqr_factor_1d_host", "num_iter must be 1 or 2");
   const size_t bytes = (size_t)m_loc * n * sizeof(double);
-  double *dA, *dQ, *dR;
+  const size_t nn = (size_t)n * n;
+  double *dA, *dQ, *dR, *ws;
   CAP_TRY(cap_workspace(h, CAP_WS_STAGE0, bytes, &dA));
   CAP_TRY(cap_workspace(h, CAP_WS_STAGE1, bytes, &dQ));
-  CAP_TRY(cap_workspace(h, CAP_WS_FACTOR, (size_t)n * n * sizeof(double), &dR));
-  CUDA_TRY(cudaMemcpyAsync(dA, A_host, bytes, cudaMemcpyHostToDevice, h->stream));
-  CAP_TRY(cap_cacqr_factor_1d(h, comm, m_loc, n, dA, m_loc, dQ, m_loc, dR, n, num_iter));
-  CUDA_TRY(cudaMemcpyAsync(Q_host, dQ, bytes, cudaMemcpyDeviceToHost, h->stream));
-  CUDA_TRY(cudaMemcpyAsync(R_host, dR, (size_t)n * n * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+  CAP_TRY(cap_workspace(h, CAP_WS_FACTOR, nn * sizeof(double), &dR));
+  CAP_TRY(cap_workspace(h, CAP_WS_GRAM, (4 * nn) * sizeof(double), &ws));
+  double *G1 = ws, *G2 = ws + nn, *Rinv = ws + 2 * nn, *packed = ws + 3 * nn;
+  if (!h->ev_a) { CUDA_TRY(cudaEventCreateWithFlags(&h->ev_a, cudaEventDisableTiming)); CUDA_TRY(cudaEventCreateWithFlags(&h->ev_b, cudaEventDisableTiming)); }
+  // chunks of ~1 GiB, multiples of 128 rows (tile height), at most 32
+  int64_t rows_per = ((std::max<int64_t>(1, (int64_t)h->host_chunk_bytes / (n * 8)) + 127) / 128) * 128;
+  if ((m_loc + rows_per - 1) / rows_per > 32) rows_per = (((m_loc + 31) / 32 + 127) / 128) * 128;
+  const int nchunks = m_loc > 0 ? (int)((m_loc + rows_per - 1) / rows_per) : 0;
+  cudaStream_t cs = h->copy_stream;
+  CUDA_TRY(cudaEventRecord(h->ev_b, h->stream));            // staging buffers may still be in use by earlier work
+  CUDA_TRY(cudaStreamWaitEvent(cs, h->ev_b, 0));
+  CAP_TRY(memset2d(h, G1, n, n, n));
+  for (int c = 0; c < nchunks; ++c) {
+    const int64_t r0 = c * rows_per, rows = std::min<int64_t>(rows_per, m_loc - r0);
+    CUDA_TRY(cudaMemcpy2DAsync(dA + r0, (size_t)m_loc * 8, A_host + r0, (size_t)lda * 8, (size_t)rows * 8, (size_t)n, cudaMemcpyHostToDevice, cs));
+    CUDA_TRY(cudaEventRecord(h->ev_a, cs));
+    CUDA_TRY(cudaStreamWaitEvent(h->stream, h->ev_a, 0));
+    CAP_TRY(cap_dsyrk(h, 'U', 'T', n, rows, 1.0, dA + r0, m_loc, c == 0 ? 0.0 : 1.0, G1, n));
+  }
+  auto finish_gram = [&](double* G) -> int {
+    if (comm) {
+      CAP_TRY(cap_pack_upper(h, packed, G, n, (int)n));
+      CAP_TRY(cap_allreduce_sum(h, comm, packed, n * (n + 1) / 2));
+      CAP_TRY(cap_unpack_upper(h, G, n, packed, (int)n, 0));
+    }
+    return cap_dcholinv(h, (int)n, G, n, Rinv, n, 1);
+  };
+  CAP_TRY(finish_gram(G1));
+  if (num_iter == 1) {
+    CAP_TRY(copy2d(h, dR, n, G1, n, n, n, 3));
+  } else {
+    CAP_TRY(cap_cqr_apply(h, m_loc, n, Rinv, n, dA, m_loc, dQ, m_loc));
+    CAP_TRY(memset2d(h, G2, n, n, n));
+    CAP_TRY(cap_cqr_gram(h, m_loc, n, dQ, m_loc, G2, n));
+    CAP_TRY(finish_gram(G2));
+    CAP_TRY(trmm_impl(h, 'R', 'U', 'N', 'N', n, n, 1.0, G1, n, G2, n, dR, n, true, false));
+  }
+  const double* src = (num_iter == 1) ? dA : dQ;
+  for (int c = 0; c < nchunks; ++c) {
+    const int64_t r0 = c * rows_per, rows = std::min<int64_t>(rows_per, m_loc - r0);
+    CAP_TRY(cap_cqr_apply(h, rows, n, Rinv, n, src + r0, m_loc, dQ + r0, m_loc));
+    CUDA_TRY(cudaEventRecord(h->ev_b, h->stream));
+    CUDA_TRY(cudaStreamWaitEvent(cs, h->ev_b, 0));
+    CUDA_TRY(cudaMemcpy2DAsync(Q_host + r0, (size_t)ldq * 8, dQ + r0, (size_t)m_loc * 8, (size_t)rows * 8, (size_t)n, cudaMemcpyDeviceToHost, cs));
+  }
+  CUDA_TRY(cudaMemcpyAsync(R_host, dR, nn * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
   CUDA_TRY(cudaStreamSynchronize(h->stream));
+  CUDA_TRY(cudaStreamSynchronize(cs));
   return CAP_OK;
 }
 

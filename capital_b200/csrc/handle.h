@@ -21,6 +21,7 @@ struct cap_handle_s {
   int* info_dev = nullptr;
   long long launches = 0;
   void* encode_tiled = nullptr;       // cuTensorMapEncodeTiled
+  size_t host_chunk_bytes = (size_t)1 << 30;   // row-chunk size of the pipelined host entry points
   int engine = 0;                     // 0 = auto (TMA engine when alignment allows), 1 = cp.async engine only
   cap_ws_slot ws[CAP_WS_SLOTS];
 };

@@ -56,6 +56,9 @@ class Engine:
         """0 = auto (TMA engine when alignment allows), 1 = cp.async engine only."""
         _lib.check(self.lib.cap_set_engine(self.h, int(engine)), "cap_set_engine")
 
+    def set_host_chunk_bytes(self, nbytes):
+        _lib.check(self.lib.cap_set_host_chunk_bytes(self.h, int(nbytes)), "cap_set_host_chunk_bytes")
+
     def close(self):
         if self.h:
             self.lib.cap_destroy(self.h)

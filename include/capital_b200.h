@@ -39,6 +39,8 @@ long long cap_kernel_launches(cap_handle_t h);               /* number of kernel
 /* tile engine selection: 0 = auto (TMA/mbarrier warp-specialised engine whenever operands are 16-byte aligned
  * with even leading dimensions, cp.async engine otherwise), 1 = cp.async engine only (A/B testing) */
 int cap_set_engine(cap_handle_t h, int engine);
+/* row-chunk size (bytes, default 1 GiB) of the pipelined host entry point cap_cacqr_factor_1d_host */
+int cap_set_host_chunk_bytes(cap_handle_t h, size_t bytes);
 
 /* ---- memory (matrix<>::_assemble / _destroy_, src/matrix/structure.hpp:4-24, matrix.hpp:158) -- */
 int cap_malloc(void** dptr, size_t bytes);
@@ -134,8 +136,9 @@ int cap_cholinv_factor(cap_handle_t h, cap_grid_t grid, int64_t n_loc, double* A
  * comm may be NULL for a single rank.  num_iter: 1 = CholeskyQR, 2 = CholeskyQR2. */
 int cap_cacqr_factor_1d(cap_handle_t h, cap_comm_t comm, int64_t m_loc, int64_t n, const double* A, int64_t lda,
                         double* Q, int64_t ldq, double* R, int64_t ldr, int num_iter);
-/* Same, end to end from HOST memory: A_host -> device (chunked, overlapped with the first Gram pass),
- * factor, Q and R -> host.  Buffers should be pinned (cap_host_alloc) for full PCIe speed. */
+/* Same, end to end from HOST memory, pipelined over row chunks on two streams: the H2D copy of A overlaps the
+ * first Gram pass, the last apply overlaps the D2H copy of Q.  Synchronises before returning.  Buffers should be
+ * pinned (cap_host_alloc) for full PCIe speed. */
 int cap_cacqr_factor_1d_host(cap_handle_t h, cap_comm_t comm, int64_t m_loc, int64_t n, const double* A_host, int64_t lda,
                              double* Q_host, int64_t ldq, double* R_host, int64_t ldr, int num_iter);
 

@@ -238,3 +238,25 @@ def test_cacqr2_full_baseline_size_properties(engine):
     rows = torch.arange(0, m, 4099, device="cuda")
     res = (torch.linalg.norm(Q[rows] @ R - A[rows]) / torch.linalg.norm(A[rows])).item()
     assert res <= TOL_RESIDUAL_PER_N * n
+
+
+@pytest.mark.parametrize("num_iter", [1, 2])
+def test_cacqr_host_entry_matches_device_path(engine, num_iter):
+    """cap_cacqr_factor_1d_host (pinned host buffers, chunked two-stream pipeline) against the device-resident call;
+    the chunk size is shrunk so that the 5000-row block is cut into several ragged chunks."""
+    import torch
+    from capital_b200.engine import colmajor
+    m, n = 5000, 96
+    A = colmajor(m, n); engine.fill_random(A, 5)
+    Q = colmajor(m, n); R = colmajor(n, n)
+    engine.cacqr_factor_1d(A, Q, R, num_iter); torch.cuda.synchronize()
+    hA = torch.empty((n, m), dtype=torch.float64, pin_memory=True); hA.copy_(A.t())
+    hQ = torch.empty((n, m), dtype=torch.float64, pin_memory=True); hR = torch.empty((n, n), dtype=torch.float64, pin_memory=True)
+    engine.set_host_chunk_bytes(1 << 20)
+    try:
+        engine.cacqr_factor_1d_host(hA, hQ, hR, m, n, num_iter)
+    finally:
+        engine.set_host_chunk_bytes(1 << 30)
+    assert relerr(hQ.t().numpy(), host(Q)) <= 1e-13
+    assert relerr(np.triu(hR.t().numpy()), np.triu(host(R))) <= 1e-13
+    assert orc.qr_orthogonality(hQ.t().numpy()) <= TOL_RESIDUAL_PER_N * n * (1 if num_iter == 2 else 1e3)
