@@ -201,6 +201,15 @@ static int gemm_launch(cap_handle_t h, GemmParams p, bool ta, bool tb, int want_
   if (p.M <= 0 || p.N <= 0) return CAP_OK;
   p.tiles_m = (p.M + BM - 1) / BM;
   p.tiles_n = (p.N + BN - 1) / BN;
+  // small products (inner levels of cholinv / trtri): one warp per 32x32 block of C, operands straight from L2
+  if (!rowpanel && h->engine == 0 && p.M <= 256 && p.N <= 256 && p.K <= 512 && (want_ksplit < 0 || want_ksplit == 1)) {
+    const dim3 grid(((p.M + 63) / 64) * ((p.N + 63) / 64));
+    p.ksplit = 1;
+    if (ta) { if (tb) dmma_small_gemm_kernel<true, true><<<grid, 128, 0, h->stream>>>(p); else dmma_small_gemm_kernel<true, false><<<grid, 128, 0, h->stream>>>(p); }
+    else    { if (tb) dmma_small_gemm_kernel<false, true><<<grid, 128, 0, h->stream>>>(p); else dmma_small_gemm_kernel<false, false><<<grid, 128, 0, h->stream>>>(p); }
+    LAUNCH_CHECK(h);
+    return CAP_OK;
+  }
   const bool tri_sq = (p.c_tri != CTRI_FULL && p.tiles_m == p.tiles_n);
   int ntiles = tri_sq ? p.tiles_m * (p.tiles_m + 1) / 2 : p.tiles_m * p.tiles_n;
   const bool tma = tma_eligible(h, p);

@@ -262,6 +262,76 @@ __global__ void __launch_bounds__(NTHREADS, 1) dmma_trmm_right_inplace_kernel(co
     }
 }
 
+// ------------------------------------------------------------------------------------------ small products
+// Products whose C has at most a few 128x128 tiles (the inner levels of cholinv / trtri) would sit on one or two
+// SMs with the big-tile engines (one 128^3 tile = 17 us at a single SM's DMMA rate).  Here one WARP owns a
+// 32x32 block of C and reads its DMMA fragments straight from global memory (the operands are L2-resident),
+// so a 128^3 product spreads over 16 warps on 4 SMs and a 256^3 one over 64 warps.  k-ranges of triangular
+// operands are applied per 32-block (finer than the 128-tile engines).  Same GemmParams, no split-K.
+template <bool TA, bool TB>
+__global__ void __launch_bounds__(128) dmma_small_gemm_kernel(const GemmParams p) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+  const int tiles_m64 = (p.M + 63) / 64;
+  const int r0 = (blockIdx.x % tiles_m64) * 64 + (warp & 1) * 32, c0 = (blockIdx.x / tiles_m64) * 64 + (warp >> 1) * 32;
+  if (r0 >= p.M || c0 >= p.N) return;
+  if (p.c_tri == CTRI_UPPER && c0 + 31 < r0) return;
+  if (p.c_tri == CTRI_LOWER && r0 + 31 < c0) return;
+  int k_begin = 0, k_end = p.K;
+  if (p.klo_mode == KR_TILE_M) k_begin = r0; else if (p.klo_mode == KR_TILE_N) k_begin = c0;
+  if (p.khi_mode == KR_TILE_M) k_end = min(p.K, r0 + 32); else if (p.khi_mode == KR_TILE_N) k_end = min(p.K, c0 + 32);
+  double acc[4][4][2];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
+  auto load = [&](int k4, double (&af)[4], double (&bf)[4]) {
+    const int k = k4 + t;
+    const bool kok = k < k_end;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int r = r0 + 8 * i + g;
+      af[i] = (kok && r < p.M) ? __ldg(TA ? p.A + (int64_t)r * p.lda + k : p.A + (int64_t)k * p.lda + r) : 0.0;
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int c = c0 + 8 * j + g;
+      bf[j] = (kok && c < p.N) ? __ldg(TB ? p.B + (int64_t)k * p.ldb + c : p.B + (int64_t)c * p.ldb + k) : 0.0;
+    }
+  };
+  double a0[4], b0[4], a1[4], b1[4];
+  if (k_begin < k_end) load(k_begin, a0, b0);
+  for (int k4 = k_begin; k4 < k_end; k4 += 8) {      // two k-steps per trip, next fragments in flight during the DMMAs
+    if (k4 + 4 < k_end) load(k4 + 4, a1, b1);
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) dmma884(acc[i][j], a0[i], b0[j]);
+    if (k4 + 4 >= k_end) break;
+    if (k4 + 8 < k_end) load(k4 + 8, a0, b0);
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) dmma884(acc[i][j], a1[i], b1[j]);
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int r = r0 + 8 * i + g;
+    if (r >= p.M) continue;
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        const int c = c0 + 8 * j + 2 * t + e;
+        if (c >= p.N) continue;
+        if (p.c_tri == CTRI_UPPER && r > c) continue;
+        if (p.c_tri == CTRI_LOWER && r < c) continue;
+        double v = p.alpha * acc[i][j][e];
+        if (p.beta != 0.0) v += p.beta * p.Cin[r + (int64_t)c * p.ldcin];
+        p.C[r + (int64_t)c * p.ldc] = v;
+      }
+  }
+}
+
 // Deterministic split-K reduction: C = alpha * sum_z part[z] + beta*C over one triangle or the full matrix.
 __global__ void splitk_reduce_kernel(const double* __restrict__ part, int64_t part_stride, int ld_part, int ksplit,
                                      double* C, int64_t ldc, int M, int N, double alpha, double beta, int c_tri) {
