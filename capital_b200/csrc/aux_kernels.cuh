@@ -1,5 +1,5 @@
 // HBM-bound helper kernels of the path (pack/unpack, copies, masks, axpby, generators); the small-block
-// Cholesky + triangular inverse lives in potrf_base.cuh.
+// Cholesky + triangular inverse lives in potrf_leaf.cuh.
 //   pack/unpack/copy          serialize<S1,S2>::invoke        (src/matrix/serialize.hpp:12-150)
 //   mask                      util::remove_triangle           (src/util/util.hpp:267-293)
 //   axpby                     summa.hpp:33,153
@@ -8,7 +8,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
-#include "potrf_base.cuh"
+#include "potrf_leaf.cuh"
 
 namespace capk {
 
