@@ -68,6 +68,10 @@ int cap_create(cap_handle_t* out, int device) {
   CUDA_TRY(cudaFuncSetAttribute(dmma_trmm_right_inplace_kernel<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES));
   CUDA_TRY(cudaFuncSetAttribute(dmma_trmm_right_inplace_kernel<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES));
   CUDA_TRY(cudaFuncSetAttribute(potrf_trtri_base_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BASE_SMEM_BYTES));
+  CUDA_TRY(cudaFuncSetAttribute(dmma_small_gemm_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMALL_SMEM_BYTES));
+  CUDA_TRY(cudaFuncSetAttribute(dmma_small_gemm_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMALL_SMEM_BYTES));
+  CUDA_TRY(cudaFuncSetAttribute(dmma_small_gemm_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMALL_SMEM_BYTES));
+  CUDA_TRY(cudaFuncSetAttribute(dmma_small_gemm_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMALL_SMEM_BYTES));
   CUDA_TRY(cudaFuncSetAttribute(dmma_tma_gemm_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, T_SMEM_BYTES));
   CUDA_TRY(cudaFuncSetAttribute(dmma_tma_gemm_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, T_SMEM_BYTES));
   CUDA_TRY(cudaFuncSetAttribute(dmma_tma_gemm_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, T_SMEM_BYTES));
@@ -202,11 +206,11 @@ static int gemm_launch(cap_handle_t h, GemmParams p, bool ta, bool tb, int want_
   p.tiles_m = (p.M + BM - 1) / BM;
   p.tiles_n = (p.N + BN - 1) / BN;
   // small products (inner levels of cholinv / trtri): one warp per 32x32 block of C, operands straight from L2
-  if (!rowpanel && h->engine == 0 && p.M <= 256 && p.N <= 256 && p.K <= 512 && (want_ksplit < 0 || want_ksplit == 1)) {
-    const dim3 grid(((p.M + 63) / 64) * ((p.N + 63) / 64));
+  if (!rowpanel && h->engine == 0 && p.M <= SMALL_MAX_MN && p.N <= SMALL_MAX_MN && p.K <= 512 && (want_ksplit < 0 || want_ksplit == 1)) {
+    const dim3 grid(((p.M + 31) / 32) * ((p.N + 31) / 32));
     p.ksplit = 1;
-    if (ta) { if (tb) dmma_small_gemm_kernel<true, true><<<grid, 128, 0, h->stream>>>(p); else dmma_small_gemm_kernel<true, false><<<grid, 128, 0, h->stream>>>(p); }
-    else    { if (tb) dmma_small_gemm_kernel<false, true><<<grid, 128, 0, h->stream>>>(p); else dmma_small_gemm_kernel<false, false><<<grid, 128, 0, h->stream>>>(p); }
+    if (ta) { if (tb) dmma_small_gemm_kernel<true, true><<<grid, SMALL_THREADS, SMALL_SMEM_BYTES, h->stream>>>(p); else dmma_small_gemm_kernel<true, false><<<grid, SMALL_THREADS, SMALL_SMEM_BYTES, h->stream>>>(p); }
+    else    { if (tb) dmma_small_gemm_kernel<false, true><<<grid, SMALL_THREADS, SMALL_SMEM_BYTES, h->stream>>>(p); else dmma_small_gemm_kernel<false, false><<<grid, SMALL_THREADS, SMALL_SMEM_BYTES, h->stream>>>(p); }
     LAUNCH_CHECK(h);
     return CAP_OK;
   }

@@ -264,71 +264,90 @@ __global__ void __launch_bounds__(NTHREADS, 1) dmma_trmm_right_inplace_kernel(co
 
 // ------------------------------------------------------------------------------------------ small products
 // Products whose C has at most a few 128x128 tiles (the inner levels of cholinv / trtri) would sit on one or two
-// SMs with the big-tile engines (one 128^3 tile = 17 us at a single SM's DMMA rate).  Here one WARP owns a
-// 32x32 block of C and reads its DMMA fragments straight from global memory (the operands are L2-resident),
-// so a 128^3 product spreads over 16 warps on 4 SMs and a 256^3 one over 64 warps.  k-ranges of triangular
-// operands are applied per 32-block (finer than the 128-tile engines).  Same GemmParams, no split-K.
+// SMs with the big-tile engines: one 128^3 tile is 17 us at a single SM's DMMA rate, and these products are what
+// the recursion spends its time in (55 % of cholinv(2048), profiles/r01_launches_cholinv2048.csv).
+// Here one CTA owns a 32x32 block of C and its 8 warps split the k-range: every warp issues ALL its DMMA
+// fragment loads up front straight from global memory (operands are L2-resident; a fragment load uses whole
+// 32-byte sectors in either storage order), runs its DMMAs, and the partial blocks are summed through shared
+// memory in a fixed order (deterministic) and stored with coalesced writes.  A 128^3 product = 16 CTAs x 8 warps
+// with 4 k-steps each.  k-ranges of triangular operands are applied per 32-block.  Same GemmParams, no split-K.
+constexpr int SMALL_MAX_MN = 256;                              // largest M, N routed here (K <= 512)
+constexpr int SMALL_THREADS = 256;
+constexpr int SMALL_BATCH = 8;                                 // k-steps (of 4) in flight per warp
+constexpr int SMALL_SMEM_BYTES = 8 * 32 * 32 * 8;              // 8 warps x 32 accumulators x 32 lanes
+
 template <bool TA, bool TB>
-__global__ void __launch_bounds__(128) dmma_small_gemm_kernel(const GemmParams p) {
+__global__ void __launch_bounds__(SMALL_THREADS) dmma_small_gemm_kernel(const GemmParams p) {
+  extern __shared__ __align__(16) double red[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
-  const int tiles_m64 = (p.M + 63) / 64;
-  const int r0 = (blockIdx.x % tiles_m64) * 64 + (warp & 1) * 32, c0 = (blockIdx.x / tiles_m64) * 64 + (warp >> 1) * 32;
-  if (r0 >= p.M || c0 >= p.N) return;
+  const int tiles_m = (p.M + 31) / 32;
+  const int r0 = (blockIdx.x % tiles_m) * 32, c0 = (blockIdx.x / tiles_m) * 32;
   if (p.c_tri == CTRI_UPPER && c0 + 31 < r0) return;
   if (p.c_tri == CTRI_LOWER && r0 + 31 < c0) return;
   int k_begin = 0, k_end = p.K;
   if (p.klo_mode == KR_TILE_M) k_begin = r0; else if (p.klo_mode == KR_TILE_N) k_begin = c0;
   if (p.khi_mode == KR_TILE_M) k_end = min(p.K, r0 + 32); else if (p.khi_mode == KR_TILE_N) k_end = min(p.K, c0 + 32);
+  const int nsteps = max(0, (k_end - k_begin + 3) / 4), per = (nsteps + 7) / 8;
+  const int s_begin = warp * per, s_end = min(nsteps, s_begin + per);
   double acc[4][4][2];
 #pragma unroll
   for (int i = 0; i < 4; ++i)
 #pragma unroll
     for (int j = 0; j < 4; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
-  auto load = [&](int k4, double (&af)[4], double (&bf)[4]) {
-    const int k = k4 + t;
-    const bool kok = k < k_end;
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int r = r0 + 8 * i + g;
-      af[i] = (kok && r < p.M) ? __ldg(TA ? p.A + (int64_t)r * p.lda + k : p.A + (int64_t)k * p.lda + r) : 0.0;
-    }
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const int c = c0 + 8 * j + g;
-      bf[j] = (kok && c < p.N) ? __ldg(TB ? p.B + (int64_t)k * p.ldb + c : p.B + (int64_t)c * p.ldb + k) : 0.0;
-    }
-  };
-  double a0[4], b0[4], a1[4], b1[4];
-  if (k_begin < k_end) load(k_begin, a0, b0);
-  for (int k4 = k_begin; k4 < k_end; k4 += 8) {      // two k-steps per trip, next fragments in flight during the DMMAs
-    if (k4 + 4 < k_end) load(k4 + 4, a1, b1);
-#pragma unroll
-    for (int i = 0; i < 4; ++i)
-#pragma unroll
-      for (int j = 0; j < 4; ++j) dmma884(acc[i][j], a0[i], b0[j]);
-    if (k4 + 4 >= k_end) break;
-    if (k4 + 8 < k_end) load(k4 + 8, a0, b0);
-#pragma unroll
-    for (int i = 0; i < 4; ++i)
-#pragma unroll
-      for (int j = 0; j < 4; ++j) dmma884(acc[i][j], a1[i], b1[j]);
-  }
+  const double* pa[4]; const double* pb[4]; bool oka[4], okb[4];
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
-    const int r = r0 + 8 * i + g;
-    if (r >= p.M) continue;
+    const int r = r0 + 8 * i + g, c = c0 + 8 * i + g;
+    oka[i] = r < p.M; okb[i] = c < p.N;
+    pa[i] = TA ? p.A + (int64_t)r * p.lda : p.A + r;           // + k (TA) or + k * lda
+    pb[i] = TB ? p.B + c : p.B + (int64_t)c * p.ldb;           // + k * ldb (TB) or + k
+  }
+  for (int sb = s_begin; sb < s_end; sb += SMALL_BATCH) {
+    double af[SMALL_BATCH][4], bf[SMALL_BATCH][4];
+#pragma unroll
+    for (int u = 0; u < SMALL_BATCH; ++u) {
+      const int k = k_begin + 4 * (sb + u) + t;
+      const bool kok = (sb + u < s_end) && k < k_end;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        af[u][i] = (kok && oka[i]) ? __ldg(TA ? pa[i] + k : pa[i] + (int64_t)k * p.lda) : 0.0;
+        bf[u][i] = (kok && okb[i]) ? __ldg(TB ? pb[i] + (int64_t)k * p.ldb : pb[i] + k) : 0.0;
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < SMALL_BATCH; ++u) {
+      if (sb + u < s_end) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) dmma884(acc[i][j], af[u][i], bf[u][j]);
+      }
+    }
+  }
+  // partial blocks -> shared memory [warp][accumulator][lane]
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
 #pragma unroll
     for (int j = 0; j < 4; ++j)
 #pragma unroll
-      for (int e = 0; e < 2; ++e) {
-        const int c = c0 + 8 * j + 2 * t + e;
-        if (c >= p.N) continue;
-        if (p.c_tri == CTRI_UPPER && r > c) continue;
-        if (p.c_tri == CTRI_LOWER && r < c) continue;
-        double v = p.alpha * acc[i][j][e];
-        if (p.beta != 0.0) v += p.beta * p.Cin[r + (int64_t)c * p.ldcin];
-        p.C[r + (int64_t)c * p.ldc] = v;
-      }
+      for (int e = 0; e < 2; ++e) red[(warp * 32 + (i * 4 + j) * 2 + e) * 32 + lane] = acc[i][j][e];
+  __syncthreads();
+  // thread -> row (tid & 31) and four columns: fixed-order sum over the warps, coalesced store
+  const int rr = threadIdx.x & 31, r = r0 + rr;
+  if (r >= p.M) return;
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    const int cc = (threadIdx.x >> 5) + 8 * q, c = c0 + cc;
+    if (c >= p.N) continue;
+    if (p.c_tri == CTRI_UPPER && r > c) continue;
+    if (p.c_tri == CTRI_LOWER && r < c) continue;
+    const int slot = (((rr >> 3) * 4 + (cc >> 3)) * 2 + (cc & 1)) * 32 + (rr & 7) * 4 + ((cc & 7) >> 1);
+    double sum = 0.0;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) sum += red[w * 1024 + slot];
+    double v = p.alpha * sum;
+    if (p.beta != 0.0) v += p.beta * p.Cin[r + (int64_t)c * p.ldcin];
+    p.C[r + (int64_t)c * p.ldc] = v;
   }
 }
 

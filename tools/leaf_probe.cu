@@ -46,17 +46,13 @@ int main(int argc, char** argv) {
       float ms; cudaEventElapsedTime(&ms, e0, e1);
 #ifdef CAPK_LEAF_PROF
       long long st[64]; cudaMemcpyFromSymbol(st, g_leaf_prof, sizeof(st));
-      printf("mode %d it %d: %.1f us | load %lld", mode, it, ms * 1e3, st[1] - st[0]);
-      const int nb = (n + 31) / 32;
-      for (int b = 0; b < nb; ++b)
-        printf(" | b%d p1 %lld p2 %lld p3 %lld", b, st[2 + 3 * b] - st[1 + 3 * b], st[3 + 3 * b] - st[2 + 3 * b], st[4 + 3 * b] - st[3 + 3 * b]);
-      printf(" | store %lld | total %lld cycles\n", st[14] - st[1 + 3 * nb], st[14] - st[0]);
-      if (st[30] > st[20]) {
-        printf("    last diag block:");
-        for (int h = 0; h < 2; ++h)
-          printf(" half%d load %lld steps %lld xstore %lld mma %lld |", h, st[21 + 5 * h] - st[20 + 5 * h], st[22 + 5 * h] - st[21 + 5 * h], st[23 + 5 * h] - st[22 + 5 * h], st[24 + 5 * h] - st[23 + 5 * h]);
-        printf(" X12 %lld | all %lld\n", st[30] - st[29], st[30] - st[20]);
-      }
+      const int nb = (n + PB - 1) / PB;
+      printf("mode %d it %d: %.1f us | load %lld |", mode, it, ms * 1e3, st[1] - st[0]);
+      for (int b = 0; b < nb; ++b) printf(" b%d %lld+%lld", b, st[2 + 2 * b] - st[1 + 2 * b], st[3 + 2 * b] - st[2 + 2 * b]);
+      printf(" | store %lld | total %lld cycles\n", st[30] - st[1 + 2 * nb], st[30] - st[0]);
+#ifdef CAPK_LEAF_REPEAT
+      printf("    S2(0) repeated: %lld %lld %lld   sweep(0) repeated: %lld %lld %lld\n", st[40] - st[2], st[41] - st[40], st[42] - st[41], st[44] - st[1], st[45] - st[44], st[46] - st[45]);
+#endif
 #else
       printf("mode %d it %d: %.1f us\n", mode, it, ms * 1e3);
 #endif
