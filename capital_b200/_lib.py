@@ -41,6 +41,7 @@ _SIGS = {
     "cap_cholinv_factor": [_ptr, _ptr, _i64, _ptr, _i64, _ptr, _i64, _int, _int, _i64],
     "cap_cacqr_factor_1d": [_ptr, _ptr, _i64, _i64, _ptr, _i64, _ptr, _i64, _ptr, _i64, _int],
     "cap_cacqr_factor_1d_host": [_ptr, _ptr, _i64, _i64, _ptr, _i64, _ptr, _i64, _ptr, _i64, _int],
+    "cap_cacqr_factor_3d": [_ptr, _ptr, _i64, _i64, _ptr, _i64, _ptr, _i64, _ptr, _i64, _ptr, _i64, _int, _int, _i64],
 }
 EXPORTS = sorted(list(_SIGS) + ["cap_last_error", "cap_get_stream", "cap_kernel_launches"])
 

@@ -395,3 +395,40 @@ int cap_cholinv_factor(cap_handle_t h, cap_grid_t g, int64_t n_loc, double* A, i
   LAUNCH_CHECK(h);
   return CAP_OK;
 }
+
+// ------------------------------------------------------------------------------------------ 3D CholeskyQR2
+// qr::cacqr::factor on a process grid (cacqr.hpp:219-248 -> invoke_3d :197-216 -> sweep_3d :77-122).
+// A, Q: local m_loc x n_loc blocks, element-cyclic over the d x d face (rows over y, columns over x), replicated
+// over depth; R (and Rinv, optional) local n_loc x n_loc blocks of the upper factor in the same distribution.
+// One sweep:  G = Q^T Q by SUMMA-syrk (the reference's row-broadcast / column-reduce / depth-broadcast of
+// cacqr.hpp:86-98 is the c == d special case of the same contraction; here the grid-transposed copy of Q travels
+// along rows and Q along columns, so every c x d x d grid works), R = chol(G) and R^-1 by the distributed cholinv,
+// Q <- Q R^-1 by SUMMA-trmm (cacqr.hpp:104-108).  Two sweeps and R = R2 R1 (cacqr.hpp:203-211) for CholeskyQR2.
+// The block back-substitution variant (`solve`, cacqr.hpp:46-73, complete_inv == 0) produces the same Q; this entry
+// point always completes the inverse.
+int cap_cacqr_factor_3d(cap_handle_t h, cap_grid_t g, int64_t m_loc, int64_t n_loc, const double* A, int64_t lda,
+                        double* Q, int64_t ldq, double* R, int64_t ldr, double* Rinv, int64_t ldri,
+                        int num_iter, int split, int64_t bc_global) {
+  if (m_loc <= 0 || n_loc <= 0 || m_loc > INT32_MAX || n_loc * g->d > INT32_MAX) return cap_fail(CAP_ERR_ARG, "cap_cacqr_factor_3d", "bad dimension");
+  if (num_iter < 1 || num_iter > 2) return cap_fail(CAP_ERR_ARG, "cap_cacqr_factor_3d", "num_iter must be 1 or 2");
+  const int64_t nn = n_loc * n_loc;
+  double* ws;
+  CAP_TRY(cap_workspace(h, CAP_WS_CQR3, (size_t)(2 * nn) * sizeof(double), &ws));
+  double* R2 = ws;
+  double* X = Rinv ? Rinv : ws + nn;
+  const int64_t ldx = Rinv ? ldri : n_loc;
+  if (Q != A) CAP_TRY(copy2d(h, Q, ldq, A, lda, m_loc, n_loc, 0));               // cacqr.hpp:226
+  for (int it = 0; it < num_iter; ++it) {
+    double* G = it == 0 ? R : R2;
+    const int64_t ldg = it == 0 ? ldr : n_loc;
+    CAP_TRY(memset2d(h, G, ldg, n_loc, n_loc));
+    CAP_TRY(cap_summa_syrk(h, g, 'U', 'T', n_loc, m_loc, 1.0, Q, ldq, nullptr, 0, 0.0, G, ldg));
+    CAP_TRY(cap_cholinv_factor(h, g, n_loc, G, ldg, X, ldx, 1, split, bc_global));
+    CAP_TRY(cap_summa_trmm(h, g, 'R', 'U', 'N', 'N', m_loc, n_loc, 1.0, X, ldx, Q, ldq));
+  }
+  if (num_iter == 2) {
+    CAP_TRY(cap_summa_trmm(h, g, 'L', 'U', 'N', 'N', n_loc, n_loc, 1.0, R2, n_loc, R, ldr));   // R = R2 R1
+  }
+  return CAP_OK;
+}
+

@@ -144,6 +144,14 @@ class Engine:
         _lib.check(self.lib.cap_cholinv_factor(self.h, grid.ptr, n, A.data_ptr(), _ld(A), Rinv.data_ptr(), _ld(Rinv),
                                                int(bool(complete_inv)), int(split), int(bc_global)), "cap_cholinv_factor")
 
+    def cacqr_factor_3d(self, grid, A, Q, R, num_iter=2, Rinv=None, split=1, bc_global=2048):
+        """qr::cacqr::factor on a process grid (cacqr.hpp:219-248, 3D branch): local m_loc x n_loc blocks."""
+        m_loc, n_loc = A.shape
+        _lib.check(self.lib.cap_cacqr_factor_3d(self.h, grid.ptr, m_loc, n_loc, A.data_ptr(), _ld(A), Q.data_ptr(), _ld(Q),
+                                                R.data_ptr(), _ld(R), Rinv.data_ptr() if Rinv is not None else None,
+                                                _ld(Rinv) if Rinv is not None else 0, int(num_iter), int(split), int(bc_global)),
+                   "cap_cacqr_factor_3d")
+
     # ---- serialize / generators -----------------------------------------------------------------
     def copy2d(self, dst, src, m, n, mode=0):
         _lib.check(self.lib.cap_copy2d(self.h, dst.data_ptr(), _ld(dst), src.data_ptr(), _ld(src), m, n, mode), "cap_copy2d")

@@ -141,6 +141,15 @@ int cap_cacqr_factor_1d(cap_handle_t h, cap_comm_t comm, int64_t m_loc, int64_t 
  * pinned (cap_host_alloc) for full PCIe speed. */
 int cap_cacqr_factor_1d_host(cap_handle_t h, cap_comm_t comm, int64_t m_loc, int64_t n, const double* A_host, int64_t lda,
                              double* Q_host, int64_t ldq, double* R_host, int64_t ldr, int num_iter);
+/* qr::cacqr::factor on a process grid: the 3D / tunable CA-CQR2 (cacqr.hpp:219-248 -> invoke_3d :197-216 ->
+ * sweep_3d :77-122; grid of topo::square / topo::rect, topology.h:16-143).  A, Q: local m_loc x n_loc blocks,
+ * element-cyclic over the d x d face (rows over y, columns over x), replicated over depth.  R: local n_loc x n_loc
+ * block of the upper factor; Rinv (may be NULL): same for the inverse factor of the LAST sweep.  Gram by SUMMA-syrk,
+ * R and R^-1 by cap_cholinv_factor (split, bc_global as there), Q <- Q R^-1 by SUMMA-trmm; always completes the
+ * inverse (the reference's complete_inv == 0 back-substitution yields the same Q). */
+int cap_cacqr_factor_3d(cap_handle_t h, cap_grid_t grid, int64_t m_loc, int64_t n_loc, const double* A, int64_t lda,
+                        double* Q, int64_t ldq, double* R, int64_t ldr, double* Rinv, int64_t ldri,
+                        int num_iter, int split, int64_t bc_global);
 
 #ifdef __cplusplus
 }

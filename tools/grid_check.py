@@ -90,6 +90,25 @@ def main():
             Xg[np.ix_(top, bot)] = 0; Xr[np.ix_(top, bot)] = 0
         report("cholinv Rinv (complete_inv=%d)" % ci, Xg, Xr)
         assert eng.info() == 0
+    # 3D CholeskyQR2 on the grid against the QR of the assembled global matrix (R unique: positive diagonal)
+    M = 8 * N
+    Atall = rng.random((M, N))
+    a_loc = loc(Atall); ml = M // d
+    for iters in (1, 2):
+        q_loc, r_loc = colmajor(ml, l), colmajor(l, l)
+        eng.reset_info()
+        eng.cacqr_factor_3d(grid, a_loc, q_loc, r_loc, iters, None, 1, max(256, N // 4)); torch.cuda.synchronize()
+        Qr, Rr = np.linalg.qr(Atall)
+        sg = np.sign(np.diag(Rr)); Qr = Qr * sg; Rr = (Rr.T * sg).T
+        Qg, Rg = gather(q_loc), gather(r_loc)
+        report("3D CQR%d R" % iters, Rg, Rr, 1e-11 if iters == 2 else 1e-9)
+        report("3D CQR%d Q" % iters, Qg, Qr, 1e-11 if iters == 2 else 1e-9)
+        orth = float(np.linalg.norm(Qg.T @ Qg - np.eye(N)))
+        good = orth <= (1e-13 * N if iters == 2 else 1e-9)
+        ok = ok and good
+        if rank == 0:
+            print("%-34s %.2e %s" % ("3D CQR%d ||Q^T Q - I||_F" % iters, orth, "ok" if good else "FAIL"), flush=True)
+        assert eng.info() == 0
     if rank == 0:
         print("GRID CHECK", "PASSED" if ok else "FAILED", "world", world, "grid %dx%dx%d" % (c, d, d), "N", N, flush=True)
     grid.close()
