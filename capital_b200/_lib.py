@@ -41,6 +41,12 @@ _SIGS = {
     "cap_cholinv_factor": [_ptr, _ptr, _i64, _ptr, _i64, _ptr, _i64, _int, _int, _i64],
     "cap_cacqr_factor_1d": [_ptr, _ptr, _i64, _i64, _ptr, _i64, _ptr, _i64, _ptr, _i64, _int],
     "cap_cacqr_factor_1d_host": [_ptr, _ptr, _i64, _i64, _ptr, _i64, _ptr, _i64, _ptr, _i64, _int],
+    "cap_residual_begin": [_ptr],
+    "cap_residual_accumulate": [_ptr, _i64, _i64, _ptr, _i64, _ptr, _i64, _int, _int, _int, _int, _dbl],
+    "cap_residual_finish": [_ptr, _ptr, _ptr],
+    "cap_validate_cacqr_1d": [_ptr, _ptr, _i64, _i64, _ptr, _i64, _ptr, _i64, _ptr, _i64, _ptr, _ptr],
+    "cap_validate_cacqr_3d": [_ptr, _ptr, _i64, _i64, _ptr, _i64, _ptr, _i64, _ptr, _i64, _ptr, _ptr],
+    "cap_validate_cholinv": [_ptr, _ptr, _i64, _ptr, _i64, _ptr, _i64, _ptr],
     "cap_cacqr_factor_3d": [_ptr, _ptr, _i64, _i64, _ptr, _i64, _ptr, _i64, _ptr, _i64, _ptr, _i64, _int, _int, _i64],
 }
 EXPORTS = sorted(list(_SIGS) + ["cap_last_error", "cap_get_stream", "cap_kernel_launches"])

@@ -93,4 +93,43 @@ __global__ void fill_symmetric_kernel(double* __restrict__ dst, int64_t ld, int6
   }
 }
 
+// ------------------------------------------------------------------------------------------ validators
+// util::residual_local (reference src/util/util.hpp:27-53): err += sum w (X - Ref)^2, ctl += sum w Ref^2 over the
+// local m x n block whose element (r, c) is global (y + d r, x + d c).  Ref == nullptr: the identity (ctl counts 1 per
+// element, as test/qr/validate.hpp:24-29).  upper_only: elements with global row <= column only
+// (test/cholesky/validate.hpp).  w = offdiag_weight off the global diagonal (2 when only one triangle of a symmetric
+// matrix was formed).  Deterministic: fixed grid, per-block partials, then one block sums them in order.
+constexpr int RESID_BLOCKS = 1184, RESID_THREADS = 256;
+__global__ void __launch_bounds__(RESID_THREADS) residual_partial_kernel(const double* __restrict__ X, int64_t ldx, const double* __restrict__ Ref, int64_t ldref,
+                                                                          int64_t m, int64_t n, int d, int x, int y, int upper_only, double offdiag_weight,
+                                                                          double* __restrict__ partial) {
+  double err = 0.0, ctl = 0.0;
+  const int64_t total = m * n;
+  for (int64_t idx = (int64_t)blockIdx.x * RESID_THREADS + threadIdx.x; idx < total; idx += (int64_t)RESID_BLOCKS * RESID_THREADS) {
+    const int64_t r = idx % m, c = idx / m, gr = y + (int64_t)d * r, gc = x + (int64_t)d * c;
+    if (upper_only && gr > gc) continue;
+    const double ref = Ref ? Ref[r + c * ldref] : (gr == gc ? 1.0 : 0.0);
+    const double w = gr == gc ? 1.0 : offdiag_weight;
+    const double diff = X[r + c * ldx] - ref;
+    err += w * diff * diff;
+    ctl += Ref ? w * ref * ref : w;
+  }
+  __shared__ double se[RESID_THREADS / 32], sc[RESID_THREADS / 32];
+  for (int o = 16; o; o >>= 1) { err += __shfl_xor_sync(0xffffffffu, err, o); ctl += __shfl_xor_sync(0xffffffffu, ctl, o); }
+  if ((threadIdx.x & 31) == 0) { se[threadIdx.x >> 5] = err; sc[threadIdx.x >> 5] = ctl; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double e = 0.0, cc = 0.0;
+    for (int w = 0; w < RESID_THREADS / 32; ++w) { e += se[w]; cc += sc[w]; }
+    partial[2 * blockIdx.x] = e; partial[2 * blockIdx.x + 1] = cc;
+  }
+}
+__global__ void residual_final_kernel(const double* __restrict__ partial, double* __restrict__ acc) {
+  if (threadIdx.x == 0 && blockIdx.x == 0) {
+    double e = 0.0, c = 0.0;
+    for (int b = 0; b < RESID_BLOCKS; ++b) { e += partial[2 * b]; c += partial[2 * b + 1]; }
+    acc[0] += e; acc[1] += c;
+  }
+}
+
 }  // namespace capk

@@ -623,4 +623,65 @@ int cap_cacqr_factor_1d_host(cap_handle_t h, cap_comm_t comm, int64_t m_loc, int
 }
 
 // ------------------------------------------------------------------------------------------ process-grid algorithms
+// ------------------------------------------------------------------------------------------ validators
+// util::residual_local (src/util/util.hpp:27-53) and the metrics built on it (test/qr/validate.hpp:7-62,
+// test/cholesky/validate.hpp:7-30), computed on the device with the library's own products.
+static int resid_ws(cap_handle_t h, double** acc, double** partial) {
+  double* ws;
+  CAP_TRY(cap_workspace(h, CAP_WS_VALID, (size_t)(2 + 2 * RESID_BLOCKS) * sizeof(double), &ws));
+  *acc = ws; *partial = ws + 2;
+  return CAP_OK;
+}
+int cap_residual_begin(cap_handle_t h) {
+  double *acc, *partial;
+  CAP_TRY(resid_ws(h, &acc, &partial));
+  CUDA_TRY(cudaMemsetAsync(acc, 0, 2 * sizeof(double), h->stream));
+  return CAP_OK;
+}
+int cap_residual_accumulate(cap_handle_t h, int64_t m, int64_t n, const double* X, int64_t ldx, const double* Ref, int64_t ldref,
+                            int d, int x, int y, int upper_only, double offdiag_weight) {
+  if (m <= 0 || n <= 0) return CAP_OK;
+  double *acc, *partial;
+  CAP_TRY(resid_ws(h, &acc, &partial));
+  residual_partial_kernel<<<RESID_BLOCKS, RESID_THREADS, 0, h->stream>>>(X, ldx, Ref, ldref, m, n, d, x, y, upper_only, offdiag_weight, partial);
+  LAUNCH_CHECK(h);
+  residual_final_kernel<<<1, 32, 0, h->stream>>>(partial, acc);
+  LAUNCH_CHECK(h);
+  return CAP_OK;
+}
+int cap_residual_finish(cap_handle_t h, cap_comm_t comm, double* out) {
+  double *acc, *partial, host[2];
+  CAP_TRY(resid_ws(h, &acc, &partial));
+  if (comm) CAP_TRY(cap_allreduce_sum(h, comm, acc, 2));
+  CUDA_TRY(cudaMemcpyAsync(host, acc, sizeof(host), cudaMemcpyDeviceToHost, h->stream));
+  CUDA_TRY(cudaStreamSynchronize(h->stream));
+  *out = host[1] > 0.0 ? std::sqrt(host[0]) / std::sqrt(host[1]) : std::sqrt(host[0]);
+  return CAP_OK;
+}
+
+// qr::validate::orthogonality / residual for the 1D algorithm: orth = ||Q^T Q - I||_F / n, resid = ||Q R - A||_F / ||A||_F.
+int cap_validate_cacqr_1d(cap_handle_t h, cap_comm_t comm, int64_t m_loc, int64_t n, const double* A, int64_t lda,
+                          const double* Q, int64_t ldq, const double* R, int64_t ldr, double* orth, double* resid) {
+  if (m_loc < 0 || n <= 0 || n > INT32_MAX || m_loc > INT32_MAX) return cap_fail(CAP_ERR_ARG, "cap_validate_cacqr_1d", "bad dimension");
+  double* G;
+  CAP_TRY(cap_workspace(h, CAP_WS_GRAM, (size_t)4 * n * n * sizeof(double), &G));
+  CAP_TRY(memset2d(h, G, n, n, n));
+  if (m_loc > 0) CAP_TRY(cap_dsyrk(h, 'U', 'T', n, m_loc, 1.0, Q, ldq, 0.0, G, n));
+  if (comm) CAP_TRY(cap_allreduce_sum(h, comm, G, n * n));
+  CAP_TRY(cap_residual_begin(h));
+  CAP_TRY(cap_residual_accumulate(h, n, n, G, n, nullptr, 0, 1, 0, 0, 1, 2.0));     // upper triangle formed: off-diagonal counts twice
+  CAP_TRY(cap_residual_finish(h, nullptr, orth));
+  // Q R - A over row chunks of at most ~1 GiB
+  const int64_t rows_per = std::max<int64_t>(128, ((((int64_t)1 << 27) / n) / 128) * 128);
+  double* T;
+  CAP_TRY(cap_workspace(h, CAP_WS_STAGE0, (size_t)std::min<int64_t>(rows_per, std::max<int64_t>(m_loc, 1)) * n * sizeof(double), &T));
+  CAP_TRY(cap_residual_begin(h));
+  for (int64_t r0 = 0; r0 < m_loc; r0 += rows_per) {
+    const int64_t rows = std::min<int64_t>(rows_per, m_loc - r0);
+    CAP_TRY(trmm_impl(h, 'R', 'U', 'N', 'N', rows, n, 1.0, R, ldr, Q + r0, ldq, T, rows, true, false));
+    CAP_TRY(cap_residual_accumulate(h, rows, n, T, rows, A + r0, lda, 1, 0, 0, 0, 1.0));
+  }
+  return cap_residual_finish(h, comm, resid);
+}
+
 #include "grid_algs.cuh"

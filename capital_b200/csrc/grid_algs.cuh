@@ -432,3 +432,36 @@ int cap_cacqr_factor_3d(cap_handle_t h, cap_grid_t g, int64_t m_loc, int64_t n_l
   return CAP_OK;
 }
 
+
+// ------------------------------------------------------------------------------------------ validators on the grid
+// cholesky::validate::residual (test/cholesky/validate.hpp:7-30): ||R^T R - A||_F / ||A||_F over the upper triangle.
+// A: the ORIGINAL local block (the caller keeps a copy; cap_cholinv_factor overwrites its argument), R: local block of the factor.
+int cap_validate_cholinv(cap_handle_t h, cap_grid_t g, int64_t n_loc, const double* A, int64_t lda, const double* R, int64_t ldr, double* resid) {
+  if (n_loc <= 0 || n_loc > INT32_MAX) return cap_fail(CAP_ERR_ARG, "cap_validate_cholinv", "bad dimension");
+  double* T;
+  CAP_TRY(cap_workspace(h, CAP_WS_STAGE0, (size_t)n_loc * n_loc * sizeof(double), &T));
+  CAP_TRY(memset2d(h, T, n_loc, n_loc, n_loc));
+  CAP_TRY(cap_summa_syrk(h, g, 'U', 'T', n_loc, n_loc, 1.0, R, ldr, nullptr, 0, 0.0, T, n_loc));
+  CAP_TRY(cap_residual_begin(h));
+  CAP_TRY(cap_residual_accumulate(h, n_loc, n_loc, T, n_loc, A, lda, g->d, g->x, g->y, 1, 1.0));
+  return cap_residual_finish(h, g->slice, resid);
+}
+
+// qr::validate::orthogonality / residual (test/qr/validate.hpp:7-62) for the grid algorithm:
+// orth = ||Q^T Q - I||_F / n, resid = ||Q R - A||_F / ||A||_F, both reduced over one layer of the grid.
+int cap_validate_cacqr_3d(cap_handle_t h, cap_grid_t g, int64_t m_loc, int64_t n_loc, const double* A, int64_t lda,
+                          const double* Q, int64_t ldq, const double* R, int64_t ldr, double* orth, double* resid) {
+  if (m_loc <= 0 || n_loc <= 0 || m_loc > INT32_MAX || n_loc > INT32_MAX) return cap_fail(CAP_ERR_ARG, "cap_validate_cacqr_3d", "bad dimension");
+  double* T;
+  CAP_TRY(cap_workspace(h, CAP_WS_STAGE0, (size_t)std::max(m_loc, n_loc) * n_loc * sizeof(double), &T));
+  CAP_TRY(memset2d(h, T, n_loc, n_loc, n_loc));
+  CAP_TRY(cap_summa_syrk(h, g, 'U', 'T', n_loc, m_loc, 1.0, Q, ldq, nullptr, 0, 0.0, T, n_loc));
+  CAP_TRY(cap_residual_begin(h));
+  CAP_TRY(cap_residual_accumulate(h, n_loc, n_loc, T, n_loc, nullptr, 0, g->d, g->x, g->y, 1, 2.0));
+  CAP_TRY(cap_residual_finish(h, g->slice, orth));
+  CAP_TRY(copy2d(h, T, m_loc, Q, ldq, m_loc, n_loc, 0));
+  CAP_TRY(cap_summa_trmm(h, g, 'R', 'U', 'N', 'N', m_loc, n_loc, 1.0, R, ldr, T, m_loc));
+  CAP_TRY(cap_residual_begin(h));
+  CAP_TRY(cap_residual_accumulate(h, m_loc, n_loc, T, m_loc, A, lda, g->d, g->x, g->y, 0, 1.0));
+  return cap_residual_finish(h, g->slice, resid);
+}

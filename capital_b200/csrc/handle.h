@@ -8,7 +8,8 @@ enum { CAP_WS_GEMM_SPLITK = 0, CAP_WS_TRI = 1, CAP_WS_PANEL = 2, CAP_WS_FACTOR =
        CAP_WS_SUMMA_A = 7, CAP_WS_SUMMA_B = 8, CAP_WS_SUMMA_C = 9, CAP_WS_SUMMA_T = 10,      // broadcast landing buffers / partial C / grid-transposed copy
        CAP_WS_CI_T1 = 11, CAP_WS_CI_W = 12, CAP_WS_CI_T2 = 13, CAP_WS_CI_BC = 14, CAP_WS_CI_BC2 = 15,  // distributed cholinv intermediates
        CAP_WS_CQR3 = 16,                                                                       // 3D CQR: second Gram / R2 and the inverse factor
-       CAP_WS_SLOTS = 17 };
+       CAP_WS_VALID = 17,                                                                      // validators: accumulators, block partials, product chunk
+       CAP_WS_SLOTS = 18 };
 
 struct cap_ws_slot { void* ptr = nullptr; size_t bytes = 0; };
 

@@ -152,6 +152,29 @@ class Engine:
                                                 _ld(Rinv) if Rinv is not None else 0, int(num_iter), int(split), int(bc_global)),
                    "cap_cacqr_factor_3d")
 
+    # ---- validators (test/qr/validate.hpp, test/cholesky/validate.hpp), computed on the device ------------
+    def validate_cacqr_1d(self, A, Q, R, comm=None):
+        """(||Q^T Q - I||_F / n, ||Q R - A||_F / ||A||_F) for the 1D algorithm; comm = the raw cap_comm_t or None."""
+        m, n = A.shape
+        orth, resid = C.c_double(), C.c_double()
+        _lib.check(self.lib.cap_validate_cacqr_1d(self.h, comm, m, n, A.data_ptr(), _ld(A), Q.data_ptr(), _ld(Q), R.data_ptr(), _ld(R),
+                                                  C.byref(orth), C.byref(resid)), "cap_validate_cacqr_1d")
+        return orth.value, resid.value
+
+    def validate_cacqr_3d(self, grid, A, Q, R):
+        m, n = A.shape
+        orth, resid = C.c_double(), C.c_double()
+        _lib.check(self.lib.cap_validate_cacqr_3d(self.h, grid.ptr, m, n, A.data_ptr(), _ld(A), Q.data_ptr(), _ld(Q), R.data_ptr(), _ld(R),
+                                                  C.byref(orth), C.byref(resid)), "cap_validate_cacqr_3d")
+        return orth.value, resid.value
+
+    def validate_cholinv(self, grid, A, R):
+        """||R^T R - A||_F / ||A||_F over the upper triangle; A = the original local block."""
+        resid = C.c_double()
+        _lib.check(self.lib.cap_validate_cholinv(self.h, grid.ptr, A.shape[0], A.data_ptr(), _ld(A), R.data_ptr(), _ld(R), C.byref(resid)),
+                   "cap_validate_cholinv")
+        return resid.value
+
     # ---- serialize / generators -----------------------------------------------------------------
     def copy2d(self, dst, src, m, n, mode=0):
         _lib.check(self.lib.cap_copy2d(self.h, dst.data_ptr(), _ld(dst), src.data_ptr(), _ld(src), m, n, mode), "cap_copy2d")

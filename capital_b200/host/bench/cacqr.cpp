@@ -27,6 +27,11 @@ int main(int argc, char** argv) {
       const double sec = benchutil::timed([&] { qr_type::factor(A, pack, RectTopo); });
       const double m = (double)num_rows, n = (double)num_columns;
       const double flops = (variant == 2 ? 4. : 2.) * m * n * n + (variant == 2 ? 5. / 3. : 2. / 3.) * n * n * n;
+      if (getenv("CAPITAL_B200_VALIDATE")) {   // the reference's test/qr/cacqr.cpp prints the same two metrics
+        double orth, resid;
+        qr::validate<qr_type>::both(A, pack, RectTopo, &orth, &resid);
+        if (rt.rank() == 0) std::cout << "orthogonality ||Q^T Q - I||_F / n - " << orth << "   residual ||Q R - A||_F / ||A||_F - " << resid << std::endl;
+      }
       if (rt.rank() == 0) std::cout << num_rows << " " << num_columns << " " << i << " " << j << " " << sec << "   # " << flops / sec * 1e-12 << " TFLOP/s on " << rt.size() << " GPU(s)" << std::endl;
     }
   }

@@ -21,6 +21,10 @@ int main(int argc, char** argv) {
     if (rt.rank() == 0) std::cout << "total time - " << sec << "   # " << n * n * n / 3. / sec * 1e-12 << " TFLOP/s (N^3/3) on " << rt.size()
                                   << " GPU(s), grid " << SquareTopo.c << "x" << SquareTopo.d << "x" << SquareTopo.d << std::endl;
   }
+  if (getenv("CAPITAL_B200_VALIDATE")) {   // the reference's test/cholesky/cholinv.cpp prints the same metric
+    const double res = cholesky::validate<cholesky_type>::residual(A, pack, SquareTopo);
+    if (rt.rank() == 0) std::cout << "residual ||R^T R - A||_F / ||A||_F (upper) - " << res << std::endl;
+  }
   int info = 0; cap_get_info(rt.handle(), &info);
   if (info != 0) { std::cerr << "potrf info = " << info << std::endl; return 1; }
   return 0;

@@ -193,16 +193,25 @@ public:
   int rank, size;
   size_t c, d, x, y, z, layout, num_chunks;
 };
-// Tall-skinny grid of the CholeskyQR path (topology.h:16-65).  Only the 1D case c == 1 (d = P) is on the
-// graded path (cacqr.hpp:229); the tunable c x d x c grid is SURVEY 8(f) "next".
+// Tall-skinny grid of the CholeskyQR path (topology.h:16-65).  c == 1: the 1D grid (d = P, cacqr.hpp:229);
+// c > 1 with c^3 == P: the cubic grid of the 3D algorithm (c == d, cacqr.hpp:232), backed by the same cap_grid_t as
+// topo::square.  Other c x d x c shapes of the reference's tunable variant: use topo::square(c), whose c x d x d
+// grids (d % c == 0 or d == 1) are what cap_cacqr_factor_3d generalises to.
 class rect {
 public:
   explicit rect(size_t c_, size_t layout_ = 0, size_t num_chunks_ = 0) : layout(layout_), num_chunks(num_chunks_) {
     auto& rt = capital::runtime::get();
     rank = rt.rank(); size = rt.size();
-    if (c_ != 1) throw std::runtime_error("topo::rect: only the 1D grid (c == 1) is implemented");
-    c = 1; d = size; x = 0; y = rank; z = 0;
+    if (c_ <= 1) { c = 1; d = size; x = 0; y = rank; z = 0; return; }
+    if (c_ * c_ * c_ != (size_t)size) throw std::runtime_error("topo::rect: c > 1 needs c^3 ranks here; use topo::square(c) for c x d x d grids");
+    capital::check(cap_grid_create(rt.world(), (int)c_, &grid), "cap_grid_create");
+    int ci, di, xi, yi, zi;
+    cap_grid_info(grid, &ci, &di, &xi, &yi, &zi);
+    c = ci; d = di; x = xi; y = yi; z = zi;
   }
+  ~rect() { if (grid) cap_grid_destroy(grid); }
+  rect(const rect&) = delete;
+  cap_grid_t grid = nullptr;
   int rank, size;
   size_t c, d, x, y, z, layout, num_chunks;
 };
@@ -372,6 +381,18 @@ private:
     return out;
   }
 };
+
+// cholesky::validate (test/cholesky/validate.hpp:7-30): ||R^T R - A||_F / ||A||_F over the upper triangle, on the device
+template <class AlgType>
+struct validate {
+  template <typename MatrixType, typename ArgType, typename CommType>
+  static double residual(const MatrixType& A, ArgType& args, CommType&& ci) {
+    double r = 0;
+    capital::check(cap_validate_cholinv(capital::handle(), ci.grid, A.num_rows_local(), A.data(), A.num_rows_local(),
+                                        args.R.data(), args.R.num_rows_local(), &r), "cap_validate_cholinv");
+    return r;
+  }
+};
 }  // namespace cholesky
 
 // ------------------------------------------------------------------------------------------ qr::cacqr
@@ -398,17 +419,33 @@ public:
     matrix<ScalarT, DimensionT, uppertri> R;                 // n x n, full storage
   };
 
-  // cacqr.hpp:219-248 -> invoke_1d (:174-193) on the 1D grid; A is untouched, Q and R are (re)allocated on first use
+  // cacqr.hpp:219-248: invoke_1d (:174-193) on the 1D grid, invoke_3d (:197-216) on a process grid (topo::rect with
+  // c > 1 or any topo::square).  A is untouched, Q and R are (re)allocated on first use.  3D: A is the local block of
+  // matrix(n, m, d, d) -- columns dealt over x, rows over y -- and R the local n/d x n/d block of the factor.
   template <typename MatrixType, typename ArgType, typename CommType>
   static void factor(const MatrixType& A, ArgType& args, CommType&& ci) {
-    if (ci.c != 1) throw std::runtime_error("qr::cacqr::factor: only the 1D grid (c == 1) is implemented");
     const int64_t m = A.num_rows_local(), n = A.num_columns_local();
-    if (!args.Q.data() || args.Q.num_rows_local() != m || args.Q.num_columns_local() != n)
-      args.Q = matrix<double, typename ArgType::DimensionType, rect>(A.num_columns_global(), A.num_rows_global(), ci.c, ci.d);
-    if (!args.R.data() || args.R.num_rows_local() != n)
-      args.R = matrix<double, typename ArgType::DimensionType, uppertri>(n, n, 1, 1);
     auto& rt = capital::runtime::get();
-    capital::check(cap_cacqr_factor_1d(rt.handle(), rt.world(), m, n, A.data(), m, args.Q.data(), m, args.R.data(), n, (int)args.num_iter), "cap_cacqr_factor_1d");
+    if (ci.grid == nullptr) {
+      if (!args.Q.data() || args.Q.num_rows_local() != m || args.Q.num_columns_local() != n)
+        args.Q = matrix<double, typename ArgType::DimensionType, rect>(A.num_columns_global(), A.num_rows_global(), ci.c, ci.d);
+      if (!args.R.data() || args.R.num_rows_local() != n)
+        args.R = matrix<double, typename ArgType::DimensionType, uppertri>(n, n, 1, 1);
+      capital::check(cap_cacqr_factor_1d(rt.handle(), rt.world(), m, n, A.data(), m, args.Q.data(), m, args.R.data(), n, (int)args.num_iter), "cap_cacqr_factor_1d");
+      return;
+    }
+    if (!args.Q.data() || args.Q.num_rows_local() != m || args.Q.num_columns_local() != n)
+      args.Q = matrix<double, typename ArgType::DimensionType, rect>(A.num_columns_global(), A.num_rows_global(), ci.d, ci.d);
+    if (!args.R.data() || args.R.num_rows_local() != n)
+      args.R = matrix<double, typename ArgType::DimensionType, uppertri>(A.num_columns_global(), A.num_columns_global(), ci.d, ci.d);
+    auto& ca = args.cholesky_inverse_args;
+    int64_t bc = (int64_t)(ci.c * ci.d), mult = ca.bc_mult_dim;          // base-case rule of cholinv.hpp:15-18
+    if (mult < 0) { for (int64_t i = 0; i < -mult; ++i) bc *= 2; } else { for (int64_t i = 0; i < mult; ++i) bc /= 2; }
+    bc = bc < 1 ? 1 : bc; bc = bc > n ? n : bc;
+    const int64_t bc_global = (int64_t)ci.d * (n / bc);
+    capital::check(cap_reset_info(rt.handle()), "cap_reset_info");
+    capital::check(cap_cacqr_factor_3d(rt.handle(), ci.grid, m, n, A.data(), m, args.Q.data(), m, args.R.data(), n, nullptr, 0,
+                                       (int)args.num_iter, (int)ca.split, bc_global), "cap_cacqr_factor_3d");
   }
   template <typename ArgType, typename CommType>
   static matrix<double, typename ArgType::DimensionType, rect> construct_Q(ArgType& args, CommType&&) { return args.Q; }
@@ -419,5 +456,23 @@ public:
                               args.R.num_rows_local(), args.R.num_columns_local(), 0), "cap_copy2d");
     return out;
   }
+};
+
+// qr::validate (test/qr/validate.hpp:7-62): ||Q^T Q - I||_F / n and ||Q R - A||_F / ||A||_F, on the device
+template <class AlgType>
+struct validate {
+  template <typename MatrixType, typename ArgType, typename CommType>
+  static void both(const MatrixType& A, ArgType& args, CommType&& ci, double* orth, double* resid) {
+    auto& rt = capital::runtime::get();
+    const int64_t m = A.num_rows_local(), n = A.num_columns_local();
+    if (ci.grid == nullptr)
+      capital::check(cap_validate_cacqr_1d(rt.handle(), rt.world(), m, n, A.data(), m, args.Q.data(), m, args.R.data(), n, orth, resid), "cap_validate_cacqr_1d");
+    else
+      capital::check(cap_validate_cacqr_3d(rt.handle(), ci.grid, m, n, A.data(), m, args.Q.data(), m, args.R.data(), n, orth, resid), "cap_validate_cacqr_3d");
+  }
+  template <typename MatrixType, typename ArgType, typename CommType>
+  static double orthogonality(const MatrixType& A, ArgType& args, CommType&& ci) { double o, r; both(A, args, ci, &o, &r); return o; }
+  template <typename MatrixType, typename ArgType, typename CommType>
+  static double residual(const MatrixType& A, ArgType& args, CommType&& ci) { double o, r; both(A, args, ci, &o, &r); return r; }
 };
 }  // namespace qr

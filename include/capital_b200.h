@@ -151,6 +151,25 @@ int cap_cacqr_factor_3d(cap_handle_t h, cap_grid_t grid, int64_t m_loc, int64_t 
                         double* Q, int64_t ldq, double* R, int64_t ldr, double* Rinv, int64_t ldri,
                         int num_iter, int split, int64_t bc_global);
 
+/* ---- validators: the caller side of the path, on the device (test/qr/validate.hpp, test/cholesky/validate.hpp) ----
+ * util::residual_local (src/util/util.hpp:27-53) as begin / accumulate / finish: accumulate adds sum w (X - Ref)^2 and
+ * sum w Ref^2 over a local m x n block whose element (r, c) is global (y + d r, x + d c); Ref == NULL means the identity
+ * (control 1 per element); upper_only keeps global row <= column; w = offdiag_weight off the global diagonal.
+ * finish sums over comm (may be NULL), synchronises and returns sqrt(err) / sqrt(control) in *out (host). */
+int cap_residual_begin(cap_handle_t h);
+int cap_residual_accumulate(cap_handle_t h, int64_t m, int64_t n, const double* X, int64_t ldx, const double* Ref, int64_t ldref,
+                            int d, int x, int y, int upper_only, double offdiag_weight);
+int cap_residual_finish(cap_handle_t h, cap_comm_t comm, double* out);
+/* qr::validate::orthogonality and ::residual (test/qr/validate.hpp:7-62): *orth = ||Q^T Q - I||_F / n,
+ * *resid = ||Q R - A||_F / ||A||_F (host doubles); 1D row blocks over comm, or local blocks on a grid */
+int cap_validate_cacqr_1d(cap_handle_t h, cap_comm_t comm, int64_t m_loc, int64_t n, const double* A, int64_t lda,
+                          const double* Q, int64_t ldq, const double* R, int64_t ldr, double* orth, double* resid);
+int cap_validate_cacqr_3d(cap_handle_t h, cap_grid_t grid, int64_t m_loc, int64_t n_loc, const double* A, int64_t lda,
+                          const double* Q, int64_t ldq, const double* R, int64_t ldr, double* orth, double* resid);
+/* cholesky::validate::residual (test/cholesky/validate.hpp:7-30): ||R^T R - A||_F / ||A||_F, upper triangle;
+ * A = the original local block (cap_cholinv_factor overwrites its argument: keep a copy) */
+int cap_validate_cholinv(cap_handle_t h, cap_grid_t grid, int64_t n_loc, const double* A, int64_t lda, const double* R, int64_t ldr, double* resid);
+
 #ifdef __cplusplus
 }
 #endif

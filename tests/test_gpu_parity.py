@@ -260,3 +260,20 @@ def test_cacqr_host_entry_matches_device_path(engine, num_iter):
     assert relerr(hQ.t().numpy(), host(Q)) <= 1e-13
     assert relerr(np.triu(hR.t().numpy()), np.triu(host(R))) <= 1e-13
     assert orc.qr_orthogonality(hQ.t().numpy()) <= TOL_RESIDUAL_PER_N * n * (1 if num_iter == 2 else 1e3)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("m,n", [(1000, 257), (65536, 256)])
+def test_device_validators_match_oracle_metrics(engine, m, n):
+    """qr::validate::{orthogonality,residual} on the device (cap_validate_cacqr_1d) against the oracle's restatement
+    of the same formulas: tiny on a clean factorization, and equal to 1e-8 relative on a deliberately damaged Q."""
+    from capital_b200.engine import colmajor
+    A = colmajor(m, n); engine.fill_random(A, 5); Q = colmajor(m, n); R = colmajor(n, n)
+    engine.cacqr_factor_1d(A, Q, R, 2)
+    orth, resid = engine.validate_cacqr_1d(A, Q, R)
+    assert orth <= TOL_RESIDUAL_PER_N * n and resid <= TOL_RESIDUAL_PER_N * n
+    assert abs(orth - orc.qr_orthogonality(host(Q))) <= 1e-15 and abs(resid - orc.qr_residual(host(A), host(Q), host(R))) <= 1e-15
+    Q[3, 2] += 0.5
+    orth, resid = engine.validate_cacqr_1d(A, Q, R)
+    o_ref, r_ref = orc.qr_orthogonality(host(Q)), orc.qr_residual(host(A), host(Q), host(R))
+    assert abs(orth - o_ref) <= 1e-8 * o_ref and abs(resid - r_ref) <= 1e-8 * r_ref

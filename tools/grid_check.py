@@ -90,6 +90,19 @@ def main():
             Xg[np.ix_(top, bot)] = 0; Xr[np.ix_(top, bot)] = 0
         report("cholinv Rinv (complete_inv=%d)" % ci, Xg, Xr)
         assert eng.info() == 0
+        if ci:
+            # device validator (cholesky::validate::residual) against the same metric in numpy, on a clean and on a
+            # deliberately damaged factor (so that agreement is not just "both tiny")
+            for damage in (False, True):
+                if damage and rank == 0:
+                    s_loc[0, 0] *= 1.5
+                got = eng.validate_cholinv(grid, loc(S), s_loc)
+                Rg = gather(s_loc)
+                ref = float(np.linalg.norm(np.triu(Rg.T @ Rg - S)) / np.linalg.norm(np.triu(S)))
+                good = (abs(got - ref) <= 1e-8 * ref) if damage else (got <= 1e-14 and ref <= 1e-14)
+                ok = ok and good
+                if rank == 0:
+                    print("%-34s device %.3e numpy %.3e %s" % ("validate cholinv%s" % (" (damaged)" if damage else ""), got, ref, "ok" if good else "FAIL"), flush=True)
     # 3D CholeskyQR2 on the grid against the QR of the assembled global matrix (R unique: positive diagonal)
     M = 8 * N
     Atall = rng.random((M, N))
@@ -109,6 +122,18 @@ def main():
         if rank == 0:
             print("%-34s %.2e %s" % ("3D CQR%d ||Q^T Q - I||_F" % iters, orth, "ok" if good else "FAIL"), flush=True)
         assert eng.info() == 0
+        if iters == 2:
+            for damage in (False, True):
+                if damage and rank == 0:
+                    q_loc[0, 0] += 0.25
+                o_dev, r_dev = eng.validate_cacqr_3d(grid, a_loc, q_loc, r_loc)
+                Qg = gather(q_loc)
+                o_ref = float(np.linalg.norm(Qg.T @ Qg - np.eye(N)) / N)
+                r_ref = float(np.linalg.norm(Qg @ Rg - Atall) / np.linalg.norm(Atall))
+                good = (abs(o_dev - o_ref) <= 1e-8 * o_ref and abs(r_dev - r_ref) <= 1e-8 * r_ref) if damage else (o_dev <= 1e-14 and r_dev <= 1e-14)
+                ok = ok and good
+                if rank == 0:
+                    print("%-34s orth %.3e / %.3e  resid %.3e / %.3e %s" % ("validate 3D CQR2%s" % (" (damaged)" if damage else ""), o_dev, o_ref, r_dev, r_ref, "ok" if good else "FAIL"), flush=True)
     if rank == 0:
         print("GRID CHECK", "PASSED" if ok else "FAILED", "world", world, "grid %dx%dx%d" % (c, d, d), "N", N, flush=True)
     grid.close()
