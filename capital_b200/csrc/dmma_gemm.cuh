@@ -271,7 +271,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) dmma_trmm_right_inplace_kernel(co
 // 32-byte sectors in either storage order), runs its DMMAs, and the partial blocks are summed through shared
 // memory in a fixed order (deterministic) and stored with coalesced writes.  A 128^3 product = 16 CTAs x 8 warps
 // with 4 k-steps each.  k-ranges of triangular operands are applied per 32-block.  Same GemmParams, no split-K.
-constexpr int SMALL_MAX_MN = 256;                              // largest M, N routed here (K <= 512)
+constexpr int SMALL_MAX_MN = 512;                              // largest M, N routed here (K <= 512)
 constexpr int SMALL_THREADS = 256;
 constexpr int SMALL_BATCH = 8;                                 // k-steps (of 4) in flight per warp
 constexpr int SMALL_SMEM_BYTES = 8 * 32 * 32 * 8;              // 8 warps x 32 accumulators x 32 lanes

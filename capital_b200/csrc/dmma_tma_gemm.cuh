@@ -221,38 +221,44 @@ __device__ __forceinline__ void lds128(double& x, double& y, uint32_t addr) {
   asm volatile("ld.shared.v2.f64 {%0, %1}, [%2+%3];" : "=d"(x), "=d"(y) : "r"(addr), "n"(IMM));
 }
 
-// Fragments of one half stage (8 k-columns = 2 DMMA k-steps e = 0, 1).
-struct Frags { double a[2][8]; double b[2][4]; };
+// Fragments of one half stage (8 k-columns = 2 DMMA k-steps e = 0, 1), split so that the software pipeline holds
+// at most 32 doubles of fragments (B of the half stage + A of one 32-row half, each double-buffered): with whole
+// half stages double-buffered (48 doubles) the consumer loop spilled ~18 registers to local memory and paid for
+// them in long-scoreboard stalls at every stage boundary (profiles/r01_ncu_full_cqr2_kernels_4194304x1024.txt).
+struct FragA { double v[2][4]; };   // [e][row tile 4R + i]
+struct FragB { double v[2][4]; };   // [e][column tile]
 
-// sbase: shared-space address of the stage (A tile, then B tile at +16 KB); H: which half of its 16 k-columns.
-template <bool A_KC, bool B_KC, int H>
-__device__ __forceinline__ void load_frags(uint32_t sbase, const FragAddr& f, Frags& fr) {
-  if (A_KC) {   // a[0][i] = k 8h+2t, a[1][i] = k 8h+2t+1 of row tile i
+// sbase: shared-space address of the stage (A tile, then B tile at +16 KB); H: which half of its 16 k-columns;
+// R: which 32-row half of the warp's 64 rows.
+template <bool A_KC, int H, int R>
+__device__ __forceinline__ void load_a(uint32_t sbase, const FragAddr& f, FragA& fr) {
+  if (A_KC) {   // v[0][i] = k 8h+2t, v[1][i] = k 8h+2t+1 of row tile 4R+i
     const uint32_t aa = sbase + f.a[H];
-    lds128<0 * 1024>(fr.a[0][0], fr.a[1][0], aa); lds128<1 * 1024>(fr.a[0][1], fr.a[1][1], aa);
-    lds128<2 * 1024>(fr.a[0][2], fr.a[1][2], aa); lds128<3 * 1024>(fr.a[0][3], fr.a[1][3], aa);
-    lds128<4 * 1024>(fr.a[0][4], fr.a[1][4], aa); lds128<5 * 1024>(fr.a[0][5], fr.a[1][5], aa);
-    lds128<6 * 1024>(fr.a[0][6], fr.a[1][6], aa); lds128<7 * 1024>(fr.a[0][7], fr.a[1][7], aa);
-  } else {      // a[e][2j], a[e][2j+1] = rows 16j+2g, 16j+2g+1 at k 8h+2t+e
+    lds128<(4 * R + 0) * 1024>(fr.v[0][0], fr.v[1][0], aa); lds128<(4 * R + 1) * 1024>(fr.v[0][1], fr.v[1][1], aa);
+    lds128<(4 * R + 2) * 1024>(fr.v[0][2], fr.v[1][2], aa); lds128<(4 * R + 3) * 1024>(fr.v[0][3], fr.v[1][3], aa);
+  } else {      // v[e][2jl], v[e][2jl+1] = rows 16j+2g, 16j+2g+1 (j = 2R + jl) at k 8h+2t+e
 #pragma unroll
     for (int e = 0; e < 2; ++e) {
       const uint32_t aa = sbase + f.a[e];
-      lds128<H * 1024 + 0 * 2048>(fr.a[e][0], fr.a[e][1], aa); lds128<H * 1024 + 1 * 2048>(fr.a[e][2], fr.a[e][3], aa);
-      lds128<H * 1024 + 2 * 2048>(fr.a[e][4], fr.a[e][5], aa); lds128<H * 1024 + 3 * 2048>(fr.a[e][6], fr.a[e][7], aa);
+      lds128<H * 1024 + (2 * R + 0) * 2048>(fr.v[e][0], fr.v[e][1], aa);
+      lds128<H * 1024 + (2 * R + 1) * 2048>(fr.v[e][2], fr.v[e][3], aa);
     }
   }
-  if (B_KC) {   // b[0][2q+y], b[1][2q+y]: column tile y of pair q
+}
+template <bool B_KC, int H>
+__device__ __forceinline__ void load_b(uint32_t sbase, const FragAddr& f, FragB& fr) {
+  if (B_KC) {   // v[0][2q+y], v[1][2q+y]: column tile y of pair q
 #pragma unroll
     for (int q = 0; q < 2; ++q) {
       const uint32_t bb = sbase + f.b[2 * q + H];
-      lds128<0>(fr.b[0][2 * q], fr.b[1][2 * q], bb);
-      lds128<1024>(fr.b[0][2 * q + 1], fr.b[1][2 * q + 1], bb);
+      lds128<0>(fr.v[0][2 * q], fr.v[1][2 * q], bb);
+      lds128<1024>(fr.v[0][2 * q + 1], fr.v[1][2 * q + 1], bb);
     }
-  } else {      // b[e][2q], b[e][2q+1] = columns 16*pair+2g, +1 at k 8h+2t+e
+  } else {      // v[e][2q], v[e][2q+1] = columns 16*pair+2g, +1 at k 8h+2t+e
 #pragma unroll
     for (int q = 0; q < 2; ++q)
 #pragma unroll
-      for (int e = 0; e < 2; ++e) lds128<H * 1024>(fr.b[e][2 * q], fr.b[e][2 * q + 1], sbase + f.b[2 * q + e]);
+      for (int e = 0; e < 2; ++e) lds128<H * 1024>(fr.v[e][2 * q], fr.v[e][2 * q + 1], sbase + f.b[2 * q + e]);
   }
 }
 
@@ -283,24 +289,28 @@ __device__ __forceinline__ void dmma_block4(double (&c00)[2], double (&c01)[2], 
       : "d"(a0), "d"(a1), "d"(b0), "d"(b1), "r"(on));
 }
 
-__device__ __forceinline__ void mma_frags(double (&acc)[8][4][2], const Frags& fr, uint32_t mask) {
+// The DMMAs of one half stage on the 32-row half R of the warp's 64 x 32 accumulator block.
+template <int R>
+__device__ __forceinline__ void mma_part(double (&acc)[8][4][2], const FragA& fa, const FragB& fb, uint32_t mask) {
   if (mask == 0xFFu) {
 #pragma unroll
     for (int e = 0; e < 2; ++e)
 #pragma unroll
-      for (int i = 0; i < 8; ++i)
+      for (int i = 0; i < 4; ++i)
 #pragma unroll
-        for (int jj = 0; jj < 4; ++jj) dmma884(acc[i][jj], fr.a[e][i], fr.b[e][jj]);
-  } else if (mask != 0u) {
+        for (int jj = 0; jj < 4; ++jj) dmma884(acc[4 * R + i][jj], fa.v[e][i], fb.v[e][jj]);
+  } else if (((mask >> (4 * R)) & 0xFu) != 0u) {
     // e outermost: the two updates of an accumulator are as far apart as the active blocks allow
 #pragma unroll
     for (int e = 0; e < 2; ++e)
 #pragma unroll
-      for (int j = 0; j < 4; ++j)
+      for (int jl = 0; jl < 2; ++jl)
 #pragma unroll
-        for (int q = 0; q < 2; ++q)
+        for (int q = 0; q < 2; ++q) {
+          const int j = 2 * R + jl;
           dmma_block4(acc[2 * j][2 * q], acc[2 * j][2 * q + 1], acc[2 * j + 1][2 * q], acc[2 * j + 1][2 * q + 1],
-                      fr.a[e][2 * j], fr.a[e][2 * j + 1], fr.b[e][2 * q], fr.b[e][2 * q + 1], (mask >> (j * 2 + q)) & 1u);
+                      fa.v[e][2 * jl], fa.v[e][2 * jl + 1], fb.v[e][2 * q], fb.v[e][2 * q + 1], (mask >> (j * 2 + q)) & 1u);
+        }
   }
 }
 
@@ -421,12 +431,16 @@ dmma_tma_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_cons
 #pragma unroll
         for (int jj = 0; jj < 4; ++jj) acc[i][jj][0] = acc[i][jj][1] = 0.0;
       const uint32_t tile_mask = (p.c_tri != CTRI_FULL && ti.tm == ti.tn) ? ctri_mask(p.c_tri, wm, wn) : 0xFFu;
-      // software pipeline: the fragments of the next half stage are in flight while the DMMAs of the
-      // current one issue (the 8 warps run in lockstep, so un-overlapped LDS bursts would idle the pipe)
-      Frags f0, f1;
+      // software pipeline in quarter stages (half of the k-columns x half of the rows): the next quarter's
+      // fragments are in flight while the DMMAs of the current one issue (the 8 warps run in lockstep, so
+      // un-overlapped LDS bursts would idle the pipe)
+      FragA a0, a1;
+      FragB b0, b1;
       if (ti.nk > 0) {
         mbar_wait(&full_bar[stage], phase);
-        load_frags<A_KC, B_KC, 0>(tiles_u32 + stage * T_STAGE_BYTES, fa, f0);
+        const uint32_t sb = tiles_u32 + stage * T_STAGE_BYTES;
+        load_b<B_KC, 0>(sb, fa, b0);
+        load_a<A_KC, 0, 0>(sb, fa, a0);
       }
       for (int kt = 0; kt < ti.nk; ++kt) {
         uint32_t mask = tile_mask;
@@ -435,15 +449,23 @@ dmma_tma_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_cons
           const int ds = (k0 - ti.diag_origin) / BK;   // 16-row step inside the diagonal block
           if (k0 >= ti.diag_origin && ds < BM / BK) mask &= diag_mask(p.diag, ds, wm, wn);
         }
-        load_frags<A_KC, B_KC, 1>(tiles_u32 + stage * T_STAGE_BYTES, fa, f1);
-        mma_frags(acc, f0, mask);
+        const uint32_t sb = tiles_u32 + stage * T_STAGE_BYTES;
+        load_a<A_KC, 0, 1>(sb, fa, a1);
+        mma_part<0>(acc, a0, b0, mask);
+        load_b<B_KC, 1>(sb, fa, b1);
+        load_a<A_KC, 1, 0>(sb, fa, a0);
+        mma_part<1>(acc, a1, b0, mask);
+        load_a<A_KC, 1, 1>(sb, fa, a1);
+        mma_part<0>(acc, a0, b1, mask);
         const int cur = stage;
         if (++stage == T_STAGES) { stage = 0; phase ^= 1u; }
         if (kt + 1 < ti.nk) {
           mbar_wait(&full_bar[stage], phase);
-          load_frags<A_KC, B_KC, 0>(tiles_u32 + stage * T_STAGE_BYTES, fa, f0);
+          const uint32_t sn = tiles_u32 + stage * T_STAGE_BYTES;
+          load_b<B_KC, 0>(sn, fa, b0);
+          load_a<A_KC, 0, 0>(sn, fa, a0);
         }
-        mma_frags(acc, f1, mask);
+        mma_part<1>(acc, a1, b1, mask);
         __syncwarp();
         if (lane == 0) mbar_arrive(&empty_bar[cur]);
       }
