@@ -92,6 +92,8 @@ __device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* m
 // alternating directions so that a panel block is re-read while it is still in L2); the diagonal 128-block
 // of a triangular operand starts at k = diag_origin.
 struct TileInfo { int tm, tn, kz, k_first, k_step, nk, diag_origin; };
+struct TrueTag { static constexpr bool value = true; };
+struct FalseTag { static constexpr bool value = false; };
 
 __device__ __forceinline__ TileInfo decode_tile(const TmaGemmParams& p, int unit, int sub) {
   TileInfo t;
@@ -291,15 +293,52 @@ __device__ __forceinline__ void dmma_block4(double (&c00)[2], double (&c01)[2], 
 
 // The DMMAs of one half stage on the 32-row half R of the warp's 64 x 32 accumulator block.
 template <int R>
-__device__ __forceinline__ void mma_part(double (&acc)[8][4][2], const FragA& fa, const FragB& fb, uint32_t mask) {
-  if (mask == 0xFFu) {
+__device__ __forceinline__ void mma_full(double (&acc)[8][4][2], const FragA& fa, const FragB& fb) {
+#pragma unroll
+  for (int e = 0; e < 2; ++e)
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int jj = 0; jj < 4; ++jj) dmma884(acc[4 * R + i][jj], fa.v[e][i], fb.v[e][jj]);
+}
+// Masked variant, only used by the separate loop over the k-stages that touch a diagonal block (and by triangular
+// C tiles).  mask bit (j*2+q): row group j (16 rows) x column pair q.  Triangular operands produce one of a few
+// shapes per half -- everything, one row group, one column pair, nothing -- each with straight-line code behind a
+// warp-uniform branch; anything else goes block by block.
+template <int R>
+__device__ __forceinline__ void mma_masked(double (&acc)[8][4][2], const FragA& fa, const FragB& fb, uint32_t mask) {
+  const uint32_t m4 = (mask >> (4 * R)) & 0xFu;
+  if (m4 == 0xFu) {
+    mma_full<R>(acc, fa, fb);
+  } else if (m4 == 0x3u) {                        // first row group, both column pairs
+#pragma unroll
+    for (int e = 0; e < 2; ++e)
+#pragma unroll
+      for (int i = 0; i < 2; ++i)
+#pragma unroll
+        for (int jj = 0; jj < 4; ++jj) dmma884(acc[4 * R + i][jj], fa.v[e][i], fb.v[e][jj]);
+  } else if (m4 == 0xCu) {                        // second row group
+#pragma unroll
+    for (int e = 0; e < 2; ++e)
+#pragma unroll
+      for (int i = 2; i < 4; ++i)
+#pragma unroll
+        for (int jj = 0; jj < 4; ++jj) dmma884(acc[4 * R + i][jj], fa.v[e][i], fb.v[e][jj]);
+  } else if (m4 == 0x5u) {                        // column pair 0, both row groups
 #pragma unroll
     for (int e = 0; e < 2; ++e)
 #pragma unroll
       for (int i = 0; i < 4; ++i)
 #pragma unroll
-        for (int jj = 0; jj < 4; ++jj) dmma884(acc[4 * R + i][jj], fa.v[e][i], fb.v[e][jj]);
-  } else if (((mask >> (4 * R)) & 0xFu) != 0u) {
+        for (int jj = 0; jj < 2; ++jj) dmma884(acc[4 * R + i][jj], fa.v[e][i], fb.v[e][jj]);
+  } else if (m4 == 0xAu) {                        // column pair 1
+#pragma unroll
+    for (int e = 0; e < 2; ++e)
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int jj = 2; jj < 4; ++jj) dmma884(acc[4 * R + i][jj], fa.v[e][i], fb.v[e][jj]);
+  } else if (m4 != 0u) {
     // e outermost: the two updates of an accumulator are as far apart as the active blocks allow
 #pragma unroll
     for (int e = 0; e < 2; ++e)
@@ -312,6 +351,10 @@ __device__ __forceinline__ void mma_part(double (&acc)[8][4][2], const FragA& fa
                       fa.v[e][2 * jl], fa.v[e][2 * jl + 1], fb.v[e][2 * q], fb.v[e][2 * q + 1], (mask >> (j * 2 + q)) & 1u);
         }
   }
+}
+template <bool MASKED, int R>
+__device__ __forceinline__ void mma_part(double (&acc)[8][4][2], const FragA& fa, const FragB& fb, uint32_t mask) {
+  if (MASKED) mma_masked<R>(acc, fa, fb, mask); else mma_full<R>(acc, fa, fb);
 }
 
 template <bool A_KC, bool B_KC>
@@ -442,33 +485,54 @@ dmma_tma_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_cons
         load_b<B_KC, 0>(sb, fa, b0);
         load_a<A_KC, 0, 0>(sb, fa, a0);
       }
-      for (int kt = 0; kt < ti.nk; ++kt) {
-        uint32_t mask = tile_mask;
-        if (p.diag != DIAG_NONE) {
-          const int k0 = ti.k_first + kt * ti.k_step;
-          const int ds = (k0 - ti.diag_origin) / BK;   // 16-row step inside the diagonal block
-          if (k0 >= ti.diag_origin && ds < BM / BK) mask &= diag_mask(p.diag, ds, wm, wn);
+      // k-stages [d0, d1) touch the diagonal block of the triangular operand (or the whole tile is a triangular
+      // C tile): they run in their own loop so that the common loop carries no mask logic at all
+      int d0 = ti.nk, d1 = ti.nk;
+      if (tile_mask != 0xFFu) { d0 = 0; }
+      else if (p.diag != DIAG_NONE && ti.nk > 0) {
+        // stage kt covers k0 = k_first + kt * k_step; masked iff diag_origin <= k0 < diag_origin + BM
+        const int lo = ti.diag_origin, hi = ti.diag_origin + BM - BK;   // first / last masked k0
+        const int ka = ti.k_first, kb = ti.k_first + (ti.nk - 1) * ti.k_step;
+        const int kmin = ti.k_step > 0 ? ka : kb, kmax = ti.k_step > 0 ? kb : ka;
+        if (kmax >= lo && kmin <= hi) {
+          const int first_k = lo > kmin ? lo : kmin, last_k = hi < kmax ? hi : kmax;   // masked k0 range (inclusive)
+          if (ti.k_step > 0) { d0 = (first_k - ka) / BK; d1 = (last_k - ka) / BK + 1; }
+          else { d0 = (ka - last_k) / BK; d1 = (ka - first_k) / BK + 1; }
         }
-        const uint32_t sb = tiles_u32 + stage * T_STAGE_BYTES;
-        load_a<A_KC, 0, 1>(sb, fa, a1);
-        mma_part<0>(acc, a0, b0, mask);
-        load_b<B_KC, 1>(sb, fa, b1);
-        load_a<A_KC, 1, 0>(sb, fa, a0);
-        mma_part<1>(acc, a1, b0, mask);
-        load_a<A_KC, 1, 1>(sb, fa, a1);
-        mma_part<0>(acc, a0, b1, mask);
-        const int cur = stage;
-        if (++stage == T_STAGES) { stage = 0; phase ^= 1u; }
-        if (kt + 1 < ti.nk) {
-          mbar_wait(&full_bar[stage], phase);
-          const uint32_t sn = tiles_u32 + stage * T_STAGE_BYTES;
-          load_b<B_KC, 0>(sn, fa, b0);
-          load_a<A_KC, 0, 0>(sn, fa, a0);
-        }
-        mma_part<1>(acc, a1, b1, mask);
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&empty_bar[cur]);
       }
+      auto stages = [&](auto masked_tag, int kt0, int kt1) {
+        constexpr bool MASKED = decltype(masked_tag)::value;
+        for (int kt = kt0; kt < kt1; ++kt) {
+          uint32_t mask = tile_mask;
+          if (MASKED && p.diag != DIAG_NONE) {
+            const int k0 = ti.k_first + kt * ti.k_step;
+            const int ds = (k0 - ti.diag_origin) / BK;   // 16-row step inside the diagonal block
+            if (k0 >= ti.diag_origin && ds < BM / BK) mask &= diag_mask(p.diag, ds, wm, wn);
+          }
+          const uint32_t sb = tiles_u32 + stage * T_STAGE_BYTES;
+          load_a<A_KC, 0, 1>(sb, fa, a1);
+          mma_part<MASKED, 0>(acc, a0, b0, mask);
+          load_b<B_KC, 1>(sb, fa, b1);
+          load_a<A_KC, 1, 0>(sb, fa, a0);
+          mma_part<MASKED, 1>(acc, a1, b0, mask);
+          load_a<A_KC, 1, 1>(sb, fa, a1);
+          mma_part<MASKED, 0>(acc, a0, b1, mask);
+          const int cur = stage;
+          if (++stage == T_STAGES) { stage = 0; phase ^= 1u; }
+          if (kt + 1 < ti.nk) {
+            mbar_wait(&full_bar[stage], phase);
+            const uint32_t sn = tiles_u32 + stage * T_STAGE_BYTES;
+            load_b<B_KC, 0>(sn, fa, b0);
+            load_a<A_KC, 0, 0>(sn, fa, a0);
+          }
+          mma_part<MASKED, 1>(acc, a1, b1, mask);
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&empty_bar[cur]);
+        }
+      };
+      stages(FalseTag{}, 0, d0);
+      stages(TrueTag{}, d0, d1);
+      stages(FalseTag{}, d1, ti.nk);
       store_tile<A_KC, B_KC>(p, ti, acc, wm, wn, g, t);
     }
 }
