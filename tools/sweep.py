@@ -3,9 +3,9 @@
 config -> seconds / TFLOP/s is printed and written as JSON.  On a B200 the best base-case size differs radically
 from the CPU defaults, which is what this is for.
 
-    python tools/sweep.py cholinv --n 16384 --bc 0 -1 -2 -3 -4 --ci 0 1 --split 1
-    python -m torch.distributed.run --nproc-per-node 8 --master-addr 127.0.0.1 tools/sweep.py cholinv --n 32768
-    python -m torch.distributed.run --nproc-per-node 8 --master-addr 127.0.0.1 tools/sweep.py cacqr3d --m 1048576 --n 4096
+    python tools/sweep.py cholinv --N 16384 --bc 0 -1 -2 -3 -4 --ci 0 1 --split 1
+    python -m torch.distributed.run --nproc-per-node 8 --master-addr 127.0.0.1 tools/sweep.py cholinv --N 32768
+    python -m torch.distributed.run --nproc-per-node 8 --master-addr 127.0.0.1 tools/sweep.py cacqr3d --M 1048576 --N 4096
 
 Knobs (reference names): complete_inv, split, bc_mult_dim (cholinv.hpp:6-18: base case = c*d * 2^-bc_mult_dim local
 rows -> global size d * l / that), grid depth c (topo::square), num_iter (1 = CholeskyQR, 2 = CholeskyQR2)."""
@@ -51,8 +51,8 @@ def timed(fn, iters, world):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("alg", choices=["cholinv", "cacqr3d"])
-    ap.add_argument("--n", type=int, default=8192)
-    ap.add_argument("--m", type=int, default=1 << 20)
+    ap.add_argument("--N", dest="n", type=int, default=8192)
+    ap.add_argument("--M", dest="m", type=int, default=1 << 20)
     ap.add_argument("--bc", type=int, nargs="*", default=[0, -1, -2, -3, -4])
     ap.add_argument("--ci", type=int, nargs="*", default=[0, 1])
     ap.add_argument("--split", type=int, nargs="*", default=[1])
