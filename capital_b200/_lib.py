@@ -18,6 +18,8 @@ _SIGS = {
     "cap_dsyrk": [_ptr, _chr, _chr, _i64, _i64, _dbl, _ptr, _i64, _dbl, _ptr, _i64],
     "cap_dtrmm": [_ptr, _chr, _chr, _chr, _chr, _i64, _i64, _dbl, _ptr, _i64, _ptr, _i64],
     "cap_dtrmm_oop": [_ptr, _chr, _chr, _chr, _chr, _i64, _i64, _dbl, _ptr, _i64, _ptr, _i64, _ptr, _i64],
+    "cap_dtrsm": [_ptr, _chr, _chr, _chr, _chr, _i64, _i64, _dbl, _ptr, _i64, _ptr, _i64],
+    "cap_set_block_sizes": [_ptr, _int, _int],
     "cap_dpotrf": [_ptr, _chr, _int, _ptr, _int], "cap_dtrtri": [_ptr, _chr, _chr, _int, _ptr, _int],
     "cap_dcholinv": [_ptr, _int, _ptr, _i64, _ptr, _i64, _int],
     "cap_cqr_gram": [_ptr, _i64, _i64, _ptr, _i64, _ptr, _i64],

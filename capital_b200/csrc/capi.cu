@@ -400,27 +400,39 @@ static int base_case(cap_handle_t h, double* A, int64_t lda, double* X, int64_t 
   LAUNCH_CHECK(h);
   return CAP_OK;
 }
+// Every BASE_NB diagonal block of the n x n triangular T inverted in ONE launch (they are independent; inside the
+// recursion they would be a serial chain of one-CTA kernels).  X: n x n with ldx (xblock == 0), or a row of compact
+// xblock x xblock blocks with leading dimension xblock (block j = inverse of T's diagonal block j).
+static int base_case_batched_inverse(cap_handle_t h, const double* T, int64_t ldt, double* X, int64_t ldx, int n, int lower, int xblock) {
+  const int leaves = (n + BASE_NB - 1) / BASE_NB;
+  potrf_trtri_base_kernel<<<leaves, BASE_THREADS, BASE_SMEM_BYTES, h->stream>>>(
+      const_cast<double*>(T), ldt, X, ldx, n, h->info_dev, 0, 0, 1, 1, lower,
+      xblock ? xblock / BASE_NB : 1 << 30, xblock ? (int64_t)xblock * xblock : 0);
+  LAUNCH_CHECK(h);
+  return CAP_OK;
+}
 static inline int split_point(int len) { return ((len / 2 + BASE_NB - 1) / BASE_NB) * BASE_NB; }
 
 // Recursive Cholesky + inverse on one device: the schedule of cholesky::cholinv::invoke
 // (reference src/alg/cholesky/cholinv/cholinv.hpp:87-165) with a true triangular-store syrk.
 // A(off.., off..) upper -> R in place; X = Rinv (zero-initialised by the caller).  W: 2 x (len/2)^2 scratch.
-static int cholinv_rec(cap_handle_t h, double* A, int64_t lda, double* X, int64_t ldx, int off, int len, bool top, int complete_inv, double* W) {
+static int cholinv_rec(cap_handle_t h, double* A, int64_t lda, double* X, int64_t ldx, int off, int len, bool top, int complete_inv, double* W,
+                       int info_off = 0) {
   double* A11 = A + off + (int64_t)off * lda;
   double* X11 = X + off + (int64_t)off * ldx;
-  if (len <= BASE_NB) return base_case(h, A11, lda, X11, ldx, len, off, 1, 0, 0);
+  if (len <= BASE_NB) return base_case(h, A11, lda, X11, ldx, len, info_off + off, 1, 0, 0);
   const int n1 = split_point(len), n2 = len - n1;
   double* A12 = A11 + (int64_t)n1 * lda;
   double* A22 = A12 + n1;
   double* X12 = X11 + (int64_t)n1 * ldx;
   double* X22 = X12 + n1;
-  CAP_TRY(cholinv_rec(h, A, lda, X, ldx, off, n1, false, complete_inv, W));
+  CAP_TRY(cholinv_rec(h, A, lda, X, ldx, off, n1, false, complete_inv, W, info_off));
   // "trsm" (cholinv.hpp:116-121): R12 = R11^{-T} A12 through the explicit inverse
   CAP_TRY(trmm_impl(h, 'L', 'U', 'T', 'N', n1, n2, 1.0, X11, ldx, A12, lda, W, n1, true, false));
   CAP_TRY(copy2d(h, A12, lda, W, n1, n1, n2, 0));
   // trailing update (cholinv.hpp:131-134): A22 -= R12^T R12, upper triangle only
   CAP_TRY(cap_dsyrk(h, 'U', 'T', n2, n1, -1.0, W, n1, 1.0, A22, lda));
-  CAP_TRY(cholinv_rec(h, A, lda, X, ldx, off + n1, n2, false, complete_inv, W));
+  CAP_TRY(cholinv_rec(h, A, lda, X, ldx, off + n1, n2, false, complete_inv, W, info_off));
   if (!(top && !complete_inv)) {
     // inverse completion (cholinv.hpp:147-156): Rinv12 = -(Rinv11 R12) Rinv22
     double* W2 = W + (int64_t)n1 * n2;
@@ -445,22 +457,16 @@ int cap_dcholinv(cap_handle_t h, int n, double* A, int64_t lda, double* Rinv, in
   return cholinv_rec(h, A, lda, Rinv, ldri, 0, n, true, complete_inv, W);
 }
 
-int cap_dpotrf(cap_handle_t h, char uplo, int n, double* A, int lda) {
-  if (!is_u(uplo)) return cap_fail(CAP_ERR_UNSUPPORTED, "cap_dpotrf", "only uplo='U' (the reference asserts dir=='U', cholinv.hpp:9)");
-  if (n <= 0) return n == 0 ? CAP_OK : cap_fail(CAP_ERR_ARG, "cap_dpotrf", "bad dimension");
-  double* X;
-  CAP_TRY(cap_workspace(h, CAP_WS_FACTOR, (size_t)n * n * sizeof(double), &X));
-  return cap_dcholinv(h, n, A, lda, X, n, 0);
-}
-
 // X = T^{-1} by recursive block inversion; T upper (lower: mirrored).  X zero-initialised by the caller.
-static int trtri_rec(cap_handle_t h, const double* T, int64_t ldt, double* X, int64_t ldx, int off, int len, bool lower, double* W) {
+// leaves_done: the BASE_NB diagonal blocks were already inverted (base_case_batched_inverse).
+static int trtri_rec(cap_handle_t h, const double* T, int64_t ldt, double* X, int64_t ldx, int off, int len, bool lower, double* W,
+                     bool leaves_done = false) {
   const double* T11 = T + off + (int64_t)off * ldt;
   double* X11 = X + off + (int64_t)off * ldx;
-  if (len <= BASE_NB) return base_case(h, const_cast<double*>(T11), ldt, X11, ldx, len, off, 0, 1, lower ? 1 : 0);
+  if (len <= BASE_NB) return leaves_done ? CAP_OK : base_case(h, const_cast<double*>(T11), ldt, X11, ldx, len, off, 0, 1, lower ? 1 : 0);
   const int n1 = split_point(len), n2 = len - n1;
-  CAP_TRY(trtri_rec(h, T, ldt, X, ldx, off, n1, lower, W));
-  CAP_TRY(trtri_rec(h, T, ldt, X, ldx, off + n1, n2, lower, W));
+  CAP_TRY(trtri_rec(h, T, ldt, X, ldx, off, n1, lower, W, leaves_done));
+  CAP_TRY(trtri_rec(h, T, ldt, X, ldx, off + n1, n2, lower, W, leaves_done));
   double* X22 = X11 + n1 + (int64_t)n1 * ldx;
   if (!lower) {  // X12 = -(X11 T12) X22
     const double* T12 = T11 + (int64_t)n1 * ldt;
@@ -482,8 +488,139 @@ int cap_dtrtri(cap_handle_t h, char uplo, char diag, int n, double* A, int lda) 
   CAP_TRY(cap_workspace(h, CAP_WS_FACTOR, (size_t)n * n * sizeof(double), &X));
   CAP_TRY(cap_workspace(h, CAP_WS_PANEL, cholinv_scratch_doubles(n) * sizeof(double), &W));
   CAP_TRY(memset2d(h, X, n, n, n));
-  CAP_TRY(trtri_rec(h, A, lda, X, n, 0, n, lower, W));
+  // the n/128 diagonal leaves are independent: one launch instead of a serial chain of one-CTA kernels
+  CAP_TRY(base_case_batched_inverse(h, A, lda, X, n, n, lower ? 1 : 0, 0));
+  CAP_TRY(trtri_rec(h, A, lda, X, n, 0, n, lower, W, true));
   return copy2d(h, A, lda, X, n, n, n, lower ? 2 : 1);   // only the referenced triangle is overwritten (LAPACK semantics)
+}
+
+// ------------------------------------------------------------------------------------------ triangular solve
+// op(T) X = alpha B (left) or X op(T) = alpha B (right), in place on B.  Recursion on the triangular operand: solve with
+// one diagonal half, update the other half of B with the off-diagonal block on the tile engine (the flops: a plain
+// gemm), solve with the second half; a diagonal block of at most `nb` is applied through its explicit inverse
+// (a triangular multiply on the same engine), so the whole solve is tensor-pipe work.  Not a reference engine call
+// (src/blas/interface.h has no _trsm; the reference forms explicit inverses instead, cholinv.hpp:113-124) -- it is what
+// makes cap_dpotrf an N^3/3 schedule.
+struct TrsmCtx {
+  cap_handle_t h;
+  bool left, upper, trans;
+  const double* T; int64_t ldt;   // the whole triangular operand; blocks are addressed by their diagonal offset
+  const double* Xd; int nb;       // compact inverses of its nb x nb diagonal blocks: block j at Xd + j*nb*nb, ld nb
+  double* W;                      // nb x (other dimension of B): staging of the left-side leaves
+};
+static inline int block_split(int len, int nb) { return ((len / 2 + nb - 1) / nb) * nb; }
+
+// B: rows [off, off+len) of the right-hand side (left; len x other) or its columns [off, off+len) (right; other x len)
+static int trsm_rec(const TrsmCtx& c, int off, int len, double* B, int64_t ldb, int64_t other) {
+  cap_handle_t h = c.h;
+  const char uplo = c.upper ? 'U' : 'L', tr = c.trans ? 'T' : 'N';
+  if (len <= c.nb) {
+    const double* Xi = c.Xd + (int64_t)(off / c.nb) * c.nb * c.nb;
+    if (c.left) {
+      CAP_TRY(copy2d(h, c.W, len, B, ldb, len, other, 0));
+      return trmm_impl(h, 'L', uplo, tr, 'N', len, other, 1.0, Xi, c.nb, c.W, len, B, ldb, true, false);
+    }
+    return trmm_impl(h, 'R', uplo, tr, 'N', other, len, 1.0, Xi, c.nb, B, ldb, B, ldb, true, true);
+  }
+  const int n1 = block_split(len, c.nb), n2 = len - n1;
+  const double* T11 = c.T + off + (int64_t)off * c.ldt;
+  const double* Toff = c.upper ? T11 + (int64_t)n1 * c.ldt : T11 + n1;   // stored off-diagonal block: n1 x n2 (upper) or n2 x n1 (lower)
+  const bool op_lower = (c.upper == c.trans);                            // op(T) is lower triangular
+  if (c.left) {
+    double *B1 = B, *B2 = B + n1;
+    if (op_lower) {   // X1 = P11^-1 B1;  B2 -= P21 X1;  X2 = P22^-1 B2
+      CAP_TRY(trsm_rec(c, off, n1, B1, ldb, other));
+      CAP_TRY(cap_dgemm(h, tr, 'N', n2, other, n1, -1.0, Toff, c.ldt, B1, ldb, 1.0, B2, ldb));
+      return trsm_rec(c, off + n1, n2, B2, ldb, other);
+    }
+    CAP_TRY(trsm_rec(c, off + n1, n2, B2, ldb, other));   // X2 = P22^-1 B2;  B1 -= P12 X2;  X1 = P11^-1 B1
+    CAP_TRY(cap_dgemm(h, tr, 'N', n1, other, n2, -1.0, Toff, c.ldt, B2, ldb, 1.0, B1, ldb));
+    return trsm_rec(c, off, n1, B1, ldb, other);
+  }
+  double *B1 = B, *B2 = B + (int64_t)n1 * ldb;
+  if (!op_lower) {    // X1 = B1 P11^-1;  B2 -= X1 P12;  X2 = B2 P22^-1
+    CAP_TRY(trsm_rec(c, off, n1, B1, ldb, other));
+    CAP_TRY(cap_dgemm(h, 'N', tr, other, n2, n1, -1.0, B1, ldb, Toff, c.ldt, 1.0, B2, ldb));
+    return trsm_rec(c, off + n1, n2, B2, ldb, other);
+  }
+  CAP_TRY(trsm_rec(c, off + n1, n2, B2, ldb, other));     // X2 = B2 P22^-1;  B1 -= X2 P21;  X1 = B1 P11^-1
+  CAP_TRY(cap_dgemm(h, 'N', tr, other, n1, n2, -1.0, B2, ldb, Toff, c.ldt, 1.0, B1, ldb));
+  return trsm_rec(c, off, n1, B1, ldb, other);
+}
+
+static int axpby2d(cap_handle_t h, double* y, int64_t ldy, const double* x, int64_t ldx, int64_t m, int64_t n, double alpha, double beta, int tri);
+
+int cap_set_block_sizes(cap_handle_t h, int potrf_nb, int trsm_nb) {
+  if (potrf_nb < BASE_NB || potrf_nb % BASE_NB || trsm_nb < BASE_NB || trsm_nb % BASE_NB)
+    return cap_fail(CAP_ERR_ARG, "cap_set_block_sizes", "block sizes must be positive multiples of 128");
+  h->potrf_nb = potrf_nb; h->trsm_nb = trsm_nb;
+  return CAP_OK;
+}
+
+int cap_dtrsm(cap_handle_t h, char side, char uplo, char trans, char diag, int64_t m, int64_t n, double alpha,
+              const double* T, int64_t ldt, double* B, int64_t ldb) {
+  if (m < 0 || n < 0 || m > INT32_MAX || n > INT32_MAX) return cap_fail(CAP_ERR_ARG, "cap_dtrsm", "bad dimension");
+  if (is_u(diag)) return cap_fail(CAP_ERR_UNSUPPORTED, "cap_dtrsm", "unit-diagonal solve is not on the path");
+  if (m == 0 || n == 0) return CAP_OK;
+  if (alpha == 0.0) return memset2d(h, B, ldb, m, n);
+  const bool left = is_l(side), lower = is_l(uplo);
+  const int nt = (int)(left ? m : n), nb = h->trsm_nb;
+  const int64_t other = left ? n : m;
+  const int nblk = (nt + nb - 1) / nb;
+  double *Xd, *W;
+  const size_t inv_scratch = cholinv_scratch_doubles(std::min(nt, nb));
+  CAP_TRY(cap_workspace(h, CAP_WS_FACTOR, (size_t)nblk * nb * nb * sizeof(double), &Xd));
+  CAP_TRY(cap_workspace(h, CAP_WS_PANEL, std::max<size_t>(inv_scratch, left ? (size_t)std::min(nt, nb) * other : 0) * sizeof(double), &W));
+  // inverses of the nb x nb diagonal blocks: all 128-leaves in one launch, then the block products of each block
+  CUDA_TRY(cudaMemsetAsync(Xd, 0, (size_t)nblk * nb * nb * sizeof(double), h->stream));
+  CAP_TRY(base_case_batched_inverse(h, T, ldt, Xd, nb, nt, lower ? 1 : 0, nb));
+  for (int j = 0; j < nblk; ++j) {
+    const int off = j * nb, len = std::min(nb, nt - off);
+    if (len > BASE_NB) CAP_TRY(trtri_rec(h, T + off + (int64_t)off * ldt, ldt, Xd + (int64_t)j * nb * nb, nb, 0, len, lower, W, true));
+  }
+  if (alpha != 1.0) CAP_TRY(axpby2d(h, B, ldb, B, ldb, m, n, alpha, 0.0, CTRI_FULL));
+  TrsmCtx c{h, left, !lower, is_t(trans), T, ldt, Xd, nb, W};
+  return trsm_rec(c, 0, nt, B, ldb, other);
+}
+
+// lapack::engine::_potrf (src/lapack/interface.hpp:31-43), upper: A = R^T R in place, N^3/3 flops.
+//   recursion:  potrf(A11);  R12 = R11^-T A12 (trsm_rec);  A22 -= R12^T R12 (triangular syrk);  potrf(A22)
+// Diagonal blocks of at most potrf_nb are factored AND inverted by the cholinv recursion (the leaf kernel produces
+// both anyway); those inverses are exactly the leaves trsm_rec needs, so no inverse larger than potrf_nb is ever formed
+// (cap_dcholinv, the reference's schedule, forms them at every level: 5N^3/12 flops for the same R).
+struct PotrfCtx { cap_handle_t h; double* A; int64_t lda; double* Xd; int nb; double* Wleaf; double* Wtrsm; };
+static int potrf_rec(const PotrfCtx& c, int off, int len) {
+  cap_handle_t h = c.h;
+  double* A11 = c.A + off + (int64_t)off * c.lda;
+  if (len <= c.nb)
+    return cholinv_rec(h, A11, c.lda, c.Xd + (int64_t)(off / c.nb) * c.nb * c.nb, c.nb, 0, len, true, 1, c.Wleaf, off);
+  const int n1 = block_split(len, c.nb), n2 = len - n1;
+  double* A12 = A11 + (int64_t)n1 * c.lda;
+  double* A22 = A12 + n1;
+  CAP_TRY(potrf_rec(c, off, n1));
+  TrsmCtx t{h, true, true, true, c.A, c.lda, c.Xd, c.nb, c.Wtrsm};
+  CAP_TRY(trsm_rec(t, off, n1, A12, c.lda, n2));
+  CAP_TRY(cap_dsyrk(h, 'U', 'T', n2, n1, -1.0, A12, c.lda, 1.0, A22, c.lda));
+  return potrf_rec(c, off + n1, n2);
+}
+
+int cap_dpotrf(cap_handle_t h, char uplo, int n, double* A, int lda) {
+  if (!is_u(uplo)) return cap_fail(CAP_ERR_UNSUPPORTED, "cap_dpotrf", "only uplo='U' (the reference asserts dir=='U', cholinv.hpp:9)");
+  if (n <= 0) return n == 0 ? CAP_OK : cap_fail(CAP_ERR_ARG, "cap_dpotrf", "bad dimension");
+  const int nb = h->potrf_nb;
+  if (n <= nb) {   // one block: the cholinv recursion without its top-level inverse completion
+    double* X;
+    CAP_TRY(cap_workspace(h, CAP_WS_FACTOR, (size_t)n * n * sizeof(double), &X));
+    return cap_dcholinv(h, n, A, lda, X, n, 0);
+  }
+  const int nblk = (n + nb - 1) / nb;
+  const size_t leaf_scratch = cholinv_scratch_doubles(nb);
+  double *Xd, *W;
+  CAP_TRY(cap_workspace(h, CAP_WS_FACTOR, (size_t)nblk * nb * nb * sizeof(double), &Xd));
+  CAP_TRY(cap_workspace(h, CAP_WS_PANEL, (leaf_scratch + (size_t)nb * n) * sizeof(double), &W));
+  CUDA_TRY(cudaMemsetAsync(Xd, 0, (size_t)nblk * nb * nb * sizeof(double), h->stream));
+  PotrfCtx c{h, A, lda, Xd, nb, W, W + leaf_scratch};
+  return potrf_rec(c, 0, n);
 }
 
 // ------------------------------------------------------------------------------------------ serialize / util / generators

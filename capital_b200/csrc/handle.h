@@ -25,6 +25,8 @@ struct cap_handle_s {
   void* encode_tiled = nullptr;       // cuTensorMapEncodeTiled
   size_t host_chunk_bytes = (size_t)1 << 30;   // row-chunk size of the pipelined host entry points
   int engine = 0;                     // 0 = auto (TMA engine when alignment allows), 1 = cp.async engine only
+  int potrf_nb = 1024;                // cap_dpotrf: largest diagonal block factored + inverted by the cholinv recursion
+  int trsm_nb = 512;                  // cap_dtrsm: largest diagonal block applied through its explicit inverse
   cap_ws_slot ws[CAP_WS_SLOTS];
 };
 

@@ -238,7 +238,19 @@ struct PatchWalk {
 // info (device int, may be null): first non-positive pivot, 1-based, offset by info_base; 0 = ok.
 __global__ void __launch_bounds__(BASE_THREADS, 1)
 potrf_trtri_base_kernel(double* A, int64_t lda, double* Rinv, int64_t ldri, int n, int* info, int info_base,
-                        int write_r, int zero_other, int skip_potrf, int lower) {
+                        int write_r, int zero_other, int skip_potrf, int lower,
+                        int leaves_per_xblock = 1 << 30, int64_t xblock_stride = 0) {
+  // batched form (independent diagonal blocks, e.g. every leaf of a triangular inverse in one launch): CTA b takes
+  // the BASE_NB block at (b, b) * BASE_NB of an n x n matrix; its inverse goes to the same place of Rinv, or, when
+  // Rinv is a row of compact square blocks of leaves_per_xblock leaves each, to block b / leaves_per_xblock.
+  if (blockIdx.x) {
+    const int b = blockIdx.x;
+    A += (int64_t)b * BASE_NB * (lda + 1);
+    Rinv += (int64_t)(b / leaves_per_xblock) * xblock_stride + (int64_t)(b % leaves_per_xblock) * BASE_NB * (ldri + 1);
+    info_base += b * BASE_NB;
+    n -= b * BASE_NB;
+  }
+  n = n < BASE_NB ? n : BASE_NB;
   extern __shared__ __align__(16) double sh[];
   double* S = sh;
   double* XB = sh + BASE_NB * PB_SLD;

@@ -92,6 +92,14 @@ class Engine:
         _lib.check(self.lib.cap_dtrmm_oop(self.h, _c(side), _c(uplo), _c(trans), _c(diag), m, n, alpha, T.data_ptr(), _ld(T),
                                           B.data_ptr(), _ld(B), Cm.data_ptr(), _ld(Cm)), "cap_dtrmm_oop")
 
+    def trsm(self, T, B, m, n, side="L", uplo="U", trans="N", diag="N", alpha=1.0):
+        """op(T) X = alpha B (side L) or X op(T) = alpha B (side R), in place on B (cap_dtrsm)."""
+        _lib.check(self.lib.cap_dtrsm(self.h, _c(side), _c(uplo), _c(trans), _c(diag), m, n, alpha, T.data_ptr(), _ld(T),
+                                      B.data_ptr(), _ld(B)), "cap_dtrsm")
+
+    def set_block_sizes(self, potrf_nb=1024, trsm_nb=512):
+        _lib.check(self.lib.cap_set_block_sizes(self.h, int(potrf_nb), int(trsm_nb)), "cap_set_block_sizes")
+
     # ---- lapack::engine -----------------------------------------------------------------------
     def _potrf(self, A, n, uplo="U"):
         _lib.check(self.lib.cap_dpotrf(self.h, _c(uplo), n, A.data_ptr(), _ld(A)), "cap_dpotrf")

@@ -63,8 +63,21 @@ int cap_dtrmm(cap_handle_t h, char side, char uplo, char trans, char diag, int64
 int cap_dtrmm_oop(cap_handle_t h, char side, char uplo, char trans, char diag, int64_t m, int64_t n, double alpha,
                   const double* T, int64_t ldt, const double* B, int64_t ldb, double* C, int64_t ldc);
 
+/* triangular solve, in place: op(T) X = alpha*B (side 'L') or X op(T) = alpha*B (side 'R'), non-unit diagonal.  The
+ * reference's engine has no _trsm (src/blas/interface.h:57-66) -- its schedules multiply by explicit inverses
+ * (cholinv.hpp:113-124, the unfinished src/alg/trsm/diaginvert); this entry point is the solve those stand for, and the
+ * building block that makes cap_dpotrf an N^3/3 schedule: recursion on T, off-diagonal updates as plain gemms on the
+ * tile engine, diagonal blocks of at most trsm_nb applied through their inverses. */
+int cap_dtrsm(cap_handle_t h, char side, char uplo, char trans, char diag, int64_t m, int64_t n, double alpha,
+              const double* T, int64_t ldt, double* B, int64_t ldb);
+/* blocking of cap_dpotrf (largest diagonal block factored + inverted by the cholinv recursion, default 1024) and
+ * cap_dtrsm (largest diagonal block applied through its inverse, default 512); multiples of 128 */
+int cap_set_block_sizes(cap_handle_t h, int potrf_nb, int trsm_nb);
+
 /* ---- LAPACK engine (src/lapack/interface.hpp:31-58) ------------------------------------------ */
-int cap_dpotrf(cap_handle_t h, char uplo, int n, double* A, int lda);            /* 'U' only (cholinv.hpp:9) */
+/* 'U' only (cholinv.hpp:9).  N^3/3 flops: recursive potrf / trsm / triangular syrk; only diagonal blocks of at most
+ * potrf_nb are inverted (cap_dcholinv below is the reference's schedule, which inverts at every level). */
+int cap_dpotrf(cap_handle_t h, char uplo, int n, double* A, int lda);
 int cap_dtrtri(cap_handle_t h, char uplo, char diag, int n, double* A, int lda);  /* 'U' or 'L', non-unit */
 /* fused potrf + trtri as the reference always uses them (cacqr.hpp:20-22, cholinv/policy.h:199-201):
  * A(upper) <- R, Rinv(upper) <- R^-1, strict lower of Rinv zeroed.  complete_inv=0 leaves the top-level
