@@ -97,6 +97,10 @@ int cap_destroy(cap_handle_t h) {
   if (h->info_dev) cudaFree(h->info_dev);
   if (h->ev_a) cudaEventDestroy(h->ev_a);
   if (h->ev_b) cudaEventDestroy(h->ev_b);
+  if (h->panel_stream) {
+    cudaStreamDestroy(h->panel_stream);
+    cudaEventDestroy(h->ev_panel[0]); cudaEventDestroy(h->ev_panel[1]); cudaEventDestroy(h->ev_u1);
+  }
   cudaStreamDestroy(h->own_stream);
   cudaStreamDestroy(h->copy_stream);
   delete h;
@@ -226,7 +230,7 @@ static int gemm_launch(cap_handle_t h, GemmParams p, bool ta, bool tb, int want_
     ksplit = (p.K + kper - 1) / kper;
     if (ksplit > 1) {
       double* part;
-      CAP_TRY(cap_workspace(h, CAP_WS_GEMM_SPLITK, (size_t)ksplit * p.M * p.N * sizeof(double), &part));
+      CAP_TRY(cap_workspace(h, h->ws_bank ? CAP_WS_GEMM_SPLITK2 : CAP_WS_GEMM_SPLITK, (size_t)ksplit * p.M * p.N * sizeof(double), &part));
       p.k_per_split = kper; p.c_split_stride = (int64_t)p.M * p.N; p.C = part; p.ldc = p.M;
     }
   }
@@ -550,6 +554,12 @@ static int trsm_rec(const TrsmCtx& c, int off, int len, double* B, int64_t ldb, 
 
 static int axpby2d(cap_handle_t h, double* y, int64_t ldy, const double* x, int64_t ldx, int64_t m, int64_t n, double alpha, double beta, int tri);
 
+int cap_set_potrf_schedule(cap_handle_t h, int schedule) {
+  if (schedule != 0 && schedule != 1) return cap_fail(CAP_ERR_ARG, "cap_set_potrf_schedule", "0 = right-looking with look-ahead, 1 = recursive");
+  h->potrf_schedule = schedule;
+  return CAP_OK;
+}
+
 int cap_set_block_sizes(cap_handle_t h, int potrf_nb, int trsm_nb) {
   if (potrf_nb < BASE_NB || potrf_nb % BASE_NB || trsm_nb < BASE_NB || trsm_nb % BASE_NB)
     return cap_fail(CAP_ERR_ARG, "cap_set_block_sizes", "block sizes must be positive multiples of 128");
@@ -613,6 +623,7 @@ int cap_dpotrf(cap_handle_t h, char uplo, int n, double* A, int lda) {
     CAP_TRY(cap_workspace(h, CAP_WS_FACTOR, (size_t)n * n * sizeof(double), &X));
     return cap_dcholinv(h, n, A, lda, X, n, 0);
   }
+  if (h->potrf_schedule == 0) return cap_potrf_1d(h, nullptr, n, nb, A, lda);   // right-looking with look-ahead (potrf_1d.cuh)
   const int nblk = (n + nb - 1) / nb;
   const size_t leaf_scratch = cholinv_scratch_doubles(nb);
   double *Xd, *W;
@@ -822,3 +833,4 @@ int cap_validate_cacqr_1d(cap_handle_t h, cap_comm_t comm, int64_t m_loc, int64_
 }
 
 #include "grid_algs.cuh"
+#include "potrf_1d.cuh"

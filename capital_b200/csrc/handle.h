@@ -9,7 +9,9 @@ enum { CAP_WS_GEMM_SPLITK = 0, CAP_WS_TRI = 1, CAP_WS_PANEL = 2, CAP_WS_FACTOR =
        CAP_WS_CI_T1 = 11, CAP_WS_CI_W = 12, CAP_WS_CI_T2 = 13, CAP_WS_CI_BC = 14, CAP_WS_CI_BC2 = 15,  // distributed cholinv intermediates
        CAP_WS_CQR3 = 16,                                                                       // 3D CQR: second Gram / R2 and the inverse factor
        CAP_WS_VALID = 17,                                                                      // validators: accumulators, block partials, product chunk
-       CAP_WS_SLOTS = 18 };
+       CAP_WS_GEMM_SPLITK2 = 18,                                                               // split-K partials of launches on the panel stream (bank 1)
+       CAP_WS_POTRF1D = 19,                                                                    // look-ahead Cholesky: inverse block, row panels (double-buffered)
+       CAP_WS_SLOTS = 20 };
 
 struct cap_ws_slot { void* ptr = nullptr; size_t bytes = 0; };
 
@@ -20,6 +22,11 @@ struct cap_handle_s {
   cudaStream_t own_stream = nullptr;
   cudaStream_t copy_stream = nullptr; // host<->device staging for the e2e entry points
   cudaEvent_t ev_a = nullptr, ev_b = nullptr;
+  cudaStream_t panel_stream = nullptr; // look-ahead Cholesky: high-priority stream of the panel operations
+  cudaEvent_t ev_panel[2] = {nullptr, nullptr}, ev_u1 = nullptr;
+  int ws_bank = 0;                    // which split-K workspace slot gemm launches use (1 while launching on the panel stream)
+  int lookahead_reserve_sms = 16;     // SMs the trailing update leaves free while a panel runs beside it
+  int potrf_schedule = 1;             // cap_dpotrf on more than one block: 0 = right-looking with look-ahead, 1 = recursive
   int* info_dev = nullptr;
   long long launches = 0;
   void* encode_tiled = nullptr;       // cuTensorMapEncodeTiled

@@ -1,0 +1,213 @@
+// Right-looking blocked Cholesky with one-panel look-ahead, on one GPU or on P GPUs with the block columns dealt
+// out 1-D (BASELINE.json north_star: "the recursive Cholesky ... on a 2x2x2 (or 1D/2D) process grid"; SURVEY.md 8(e)
+// "1D/2D block-cyclic right-looking variant").  A = R^T R, upper, N^3/3 flops; what lapack::engine::_potrf
+// (reference src/lapack/interface.hpp:31-43) computes, scheduled for a machine where the serial part (the diagonal
+// blocks) must hide behind the tensor-pipe part (the trailing update).  Included at the end of capi.cu.
+//
+// Layout: block columns of width nb; block j belongs to round r = j / P and goes to rank (r even ? j % P : P-1 - j % P)
+// (boustrophedon: in the upper triangle a later column is a taller column; alternating the direction evens the work out),
+// where it is local block r.  A rank stores its blocks side by side as one N x (sum of widths) column-major array.
+//
+// Per panel j (two streams per rank: M = the handle's stream, P = a high-priority panel stream):
+//   panel(j)  on P   owner: R_jj and X_j = R_jj^-1 (cholinv recursion on the nb x nb block)  -> broadcast X_j
+//                    every rank: R_j,loc = X_j^T A_j,loc for its columns right of j (triangular multiply on the tile engine)
+//                    all-gather of the row panel, put in global column order (Rrow)
+//   U1(j)     on M   block row j+1 of the trailing matrix -= R_j,j+1^T R_j,:      (all that panel(j+1) needs)
+//   U2(j)     on M   the rest of the trailing matrix, per run of locally owned consecutive block columns:
+//                    a plain gemm for the rows above the run's diagonal square + a triangular syrk on the square
+// panel(j+1) is enqueued behind U1(j) and runs WHILE U2(j) runs: U2 launches its persistent tile-engine CTAs on
+// num_sms - reserve SMs so that the panel's one-CTA leaf kernels, small products and NCCL kernels have SMs to run on.
+// Buffers of consecutive panels alternate (U2(j) still reads panel j's row while panel(j+1) writes its own).
+#pragma once
+
+struct Layout1D {
+  int P, nb; int64_t N; int nblk;
+  int owner(int j) const { const int r = j / P, pos = j % P; return (r & 1) ? P - 1 - pos : pos; }
+  int global_block(int r, int p) const { return r * P + ((r & 1) ? P - 1 - p : p); }
+  int width(int j) const { return (int)std::min<int64_t>(nb, N - (int64_t)j * nb); }
+  int nloc(int p) const { int n = 0; while (global_block(n, p) < nblk) ++n; return n; }
+  // number of p's local blocks with global index <= j
+  int upto(int p, int j) const { const int rj = j / P, pos = j % P; return rj + ((((rj & 1) ? P - 1 - p : p) <= pos) ? 1 : 0); }
+  int64_t cols(int p) const { const int n = nloc(p); return n == 0 ? 0 : (int64_t)(n - 1) * nb + width(global_block(n - 1, p)); }
+  // local columns of p strictly right of block j
+  int64_t cols_right(int p, int j) const { return std::max<int64_t>(0, cols(p) - (int64_t)std::min(upto(p, j), nloc(p)) * nb); }
+};
+
+int cap_potrf_1d_layout(int64_t N, int nb, int nranks, int rank, int64_t* ncols_loc, int* nblocks_loc) {
+  if (N < 0 || nb < 1 || nranks < 1 || rank < 0 || rank >= nranks) return cap_fail(CAP_ERR_ARG, "cap_potrf_1d_layout", "bad argument");
+  Layout1D L{nranks, nb, N, (int)((N + nb - 1) / nb)};
+  if (ncols_loc) *ncols_loc = L.cols(rank);
+  if (nblocks_loc) *nblocks_loc = L.nloc(rank);
+  return CAP_OK;
+}
+int cap_potrf_1d_block(int64_t j, int nranks, int* owner, int* local_block) {
+  if (j < 0 || nranks < 1) return cap_fail(CAP_ERR_ARG, "cap_potrf_1d_block", "bad argument");
+  Layout1D L{nranks, 1, 0, 0};
+  if (owner) *owner = L.owner((int)j);
+  if (local_block) *local_block = (int)(j / nranks);
+  return CAP_OK;
+}
+
+// gathered row panel (rank-major, nb x maxcl per rank, every block nb x nb contiguous) -> global column order
+__global__ void assemble_row_panel_kernel(double* __restrict__ Rrow, const double* __restrict__ gath, int j, int P, int nb, int64_t per_rank, int64_t N) {
+  const int l = j + 1 + blockIdx.y;
+  const int r = l / P, pos = l % P, own = (r & 1) ? P - 1 - pos : pos;
+  const int rj = j / P, posj = j % P;
+  const int upto = rj + ((((rj & 1) ? P - 1 - own : own) <= posj) ? 1 : 0);
+  const int64_t w = min((int64_t)nb, N - (int64_t)l * nb);
+  const double2* src = reinterpret_cast<const double2*>(gath + own * per_rank + (int64_t)(r - upto) * nb * nb);
+  double2* dst = reinterpret_cast<double2*>(Rrow + (int64_t)blockIdx.y * nb * nb);
+  const int64_t n2 = w * nb / 2;     // nb is a multiple of 128
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n2; i += (int64_t)gridDim.x * blockDim.x) dst[i] = src[i];
+}
+
+struct StreamScope {   // every helper in this file launches on h->stream: switch it (and the split-K workspace bank) for a scope
+  cap_handle_t h; cudaStream_t saved; int saved_bank;
+  StreamScope(cap_handle_t h_, cudaStream_t s, int bank) : h(h_), saved(h_->stream), saved_bank(h_->ws_bank) { h->stream = s; h->ws_bank = bank; }
+  ~StreamScope() { h->stream = saved; h->ws_bank = saved_bank; }
+};
+struct SmCapScope {
+  cap_handle_t h; int saved;
+  SmCapScope(cap_handle_t h_, int cap) : h(h_), saved(h_->num_sms) { if (cap > 0 && cap < saved) h->num_sms = cap; }
+  ~SmCapScope() { h->num_sms = saved; }
+};
+
+struct Potrf1D {
+  cap_handle_t h; cap_comm_t comm; Layout1D L; int me;
+  double* A; int64_t lda;
+  double *X[2], *S[2], *G[2], *R[2], *Wleaf;   // inverse of the diagonal block, local row panel, gathered, ordered
+  int64_t maxcl0;
+  cudaStream_t sm, sp;
+  cudaEvent_t ev_panel[2], ev_u1;
+
+  double* blockptr(int row_block, int local_block) const { return A + (int64_t)row_block * L.nb + (int64_t)local_block * L.nb * lda; }
+
+  // ---- panel(j) on the panel stream --------------------------------------------------------------------------
+  int panel(int j) {
+    const int nb = L.nb, b = j & 1, own = L.owner(j), w = L.width(j);
+    StreamScope scope(h, sp, 1);
+    const bool last = (j == L.nblk - 1);
+    if (me == own) {
+      CUDA_TRY(cudaMemsetAsync(X[b], 0, (size_t)nb * nb * sizeof(double), h->stream));
+      CAP_TRY(cholinv_rec(h, blockptr(j, j / L.P), lda, X[b], nb, 0, w, true, last ? 0 : 1, Wleaf, j * nb));
+    }
+    if (last) return CAP_OK;                             // nothing to the right of the last block
+    CAP_TRY(cap_bcast(h, comm, X[b], (int64_t)nb * nb, own));
+    const int r0 = std::min(L.upto(me, j), L.nloc(me));
+    const int64_t ncl = L.cols_right(me, j);
+    if (ncl > 0) {                                      // R_j,loc = X_j^T A_j,loc, kept in S (the all-gather payload) and in A
+      double* Bp = blockptr(j, r0);
+      CAP_TRY(trmm_impl(h, 'L', 'U', 'T', 'N', nb, ncl, 1.0, X[b], nb, Bp, lda, S[b], nb, true, false));
+      CAP_TRY(copy2d(h, Bp, lda, S[b], nb, nb, ncl, 0));
+    }
+    if (L.P > 1) {
+      int64_t maxcl = 0;
+      for (int p = 0; p < L.P; ++p) maxcl = std::max(maxcl, L.cols_right(p, j));
+      CAP_TRY(cap_allgather(h, comm, S[b], G[b], (int64_t)nb * maxcl));
+      const int nright = L.nblk - 1 - j;
+      assemble_row_panel_kernel<<<dim3(16, nright), 256, 0, h->stream>>>(R[b], G[b], j, L.P, nb, (int64_t)nb * maxcl, L.N);
+      LAUNCH_CHECK(h);
+    }
+    return CAP_OK;
+  }
+
+  // ---- U1(j): block row j+1 of the trailing matrix (on M) ------------------------------------------------------
+  int update_next_row(int j) {
+    const int nb = L.nb, b = j & 1, k = j + 1, wk = L.width(k);
+    const int r0 = std::min(L.upto(me, j), L.nloc(me));          // first local block right of j
+    int rr = r0;
+    if (me == L.owner(k)) {                                       // diagonal block (k, k): upper triangle only
+      const double* Sk = S[b] + (int64_t)(k / L.P - r0) * nb * nb;
+      CAP_TRY(cap_dsyrk(h, 'U', 'T', wk, nb, -1.0, Sk, nb, 1.0, blockptr(k, k / L.P), lda));
+      rr = k / L.P + 1;
+    }
+    const int64_t ncl = L.cols(me) - (int64_t)std::min(rr, L.nloc(me)) * nb;
+    if (ncl > 0)
+      CAP_TRY(cap_dgemm(h, 'T', 'N', wk, ncl, nb, -1.0, R[b], nb, S[b] + (int64_t)(rr - r0) * nb * nb, nb, 1.0, blockptr(k, rr), lda));
+    return CAP_OK;
+  }
+
+  // ---- U2(j): rows >= j+2 of the trailing matrix (on M, SM-capped while a panel runs beside it) -----------------------
+  int update_rest(int j) {
+    const int nb = L.nb, b = j & 1, n = L.nloc(me);
+    const int r0 = std::min(L.upto(me, j), n);
+    int r = r0;
+    while (r < n && L.global_block(r, me) < j + 2) ++r;
+    while (r < n) {
+      int r_end = r + 1;                                          // run of consecutive global blocks [k0, k1]
+      while (r_end < n && L.global_block(r_end, me) == L.global_block(r_end - 1, me) + 1) ++r_end;
+      const int k0 = L.global_block(r, me);
+      const int64_t wrun = (int64_t)(r_end - 1 - r) * nb + L.width(L.global_block(r_end - 1, me));
+      const double* Srun = S[b] + (int64_t)(r - r0) * nb * nb;
+      const int64_t hrect = (int64_t)(k0 - j - 2) * nb;
+      if (hrect > 0)
+        CAP_TRY(cap_dgemm(h, 'T', 'N', hrect, wrun, nb, -1.0, R[b] + (int64_t)nb * nb, nb, Srun, nb, 1.0, blockptr(j + 2, r), lda));
+      CAP_TRY(cap_dsyrk(h, 'U', 'T', wrun, nb, -1.0, Srun, nb, 1.0, blockptr(k0, r), lda));
+      r = r_end;
+    }
+    return CAP_OK;
+  }
+
+  int run() {
+    const int nblk = L.nblk;
+    CAP_TRY(panel(0));
+    CUDA_TRY(cudaEventRecord(ev_panel[0], sp));
+    for (int j = 0; j < nblk; ++j) {
+      CUDA_TRY(cudaStreamWaitEvent(sm, ev_panel[j & 1], 0));
+      if (j + 1 >= nblk) break;
+      CAP_TRY(update_next_row(j));
+      CUDA_TRY(cudaEventRecord(ev_u1, sm));
+      CUDA_TRY(cudaStreamWaitEvent(sp, ev_u1, 0));
+      CAP_TRY(panel(j + 1));
+      CUDA_TRY(cudaEventRecord(ev_panel[(j + 1) & 1], sp));
+      if (j + 2 < nblk) {
+        SmCapScope cap(h, h->lookahead_reserve_sms > 0 ? h->num_sms - h->lookahead_reserve_sms : 0);
+        CAP_TRY(update_rest(j));
+      }
+    }
+    return CAP_OK;
+  }
+};
+
+int cap_set_lookahead(cap_handle_t h, int reserve_sms) {
+  if (reserve_sms < 0 || reserve_sms >= h->num_sms) return cap_fail(CAP_ERR_ARG, "cap_set_lookahead", "reserve must be in [0, #SMs)");
+  h->lookahead_reserve_sms = reserve_sms;
+  return CAP_OK;
+}
+
+int cap_potrf_1d(cap_handle_t h, cap_comm_t comm, int64_t N, int nb, double* A_loc, int64_t lda) {
+  if (N < 0 || N > INT32_MAX || nb < BASE_NB || nb % BASE_NB || lda < std::max<int64_t>(1, N)) return cap_fail(CAP_ERR_ARG, "cap_potrf_1d", "bad argument (nb: multiple of 128; lda >= N)");
+  if (N == 0) return CAP_OK;
+  int P = 1, me = 0;
+  if (comm) { cap_comm_size(comm, &P); cap_comm_rank(comm, &me); }
+  Potrf1D s{};
+  s.h = h; s.comm = P > 1 ? comm : nullptr; s.me = me; s.A = A_loc; s.lda = lda;
+  s.L = Layout1D{P, nb, N, (int)((N + nb - 1) / nb)};
+  int64_t maxcl0 = 0;
+  for (int p = 0; p < P; ++p) maxcl0 = std::max(maxcl0, s.L.cols_right(p, 0));
+  maxcl0 = std::max<int64_t>(maxcl0, 1);
+  s.maxcl0 = maxcl0;
+  const size_t xs = (size_t)nb * nb, ss = (size_t)nb * maxcl0, gs = P > 1 ? (size_t)P * ss : 0, rs = P > 1 ? (size_t)nb * std::max<int64_t>(N - nb, 1) : 0;
+  const size_t leaf = cholinv_scratch_doubles(nb);
+  double* ws;
+  CAP_TRY(cap_workspace(h, CAP_WS_POTRF1D, (2 * (xs + ss + gs + rs) + leaf) * sizeof(double), &ws));
+  for (int b = 0; b < 2; ++b) {
+    s.X[b] = ws; ws += xs;
+    s.S[b] = ws; ws += ss;
+    s.G[b] = P > 1 ? ws : nullptr; ws += gs;
+    s.R[b] = P > 1 ? ws : s.S[b]; ws += rs;      // one rank: the local row panel IS the whole row panel
+  }
+  s.Wleaf = ws;
+  if (!h->panel_stream) {
+    int lo = 0, hi = 0;
+    CUDA_TRY(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+    CUDA_TRY(cudaStreamCreateWithPriority(&h->panel_stream, cudaStreamNonBlocking, hi));
+    for (cudaEvent_t* e : {&h->ev_panel[0], &h->ev_panel[1], &h->ev_u1}) CUDA_TRY(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+  }
+  s.sm = h->stream; s.sp = h->panel_stream;
+  s.ev_panel[0] = h->ev_panel[0]; s.ev_panel[1] = h->ev_panel[1]; s.ev_u1 = h->ev_u1;
+  // the panel stream starts behind everything already enqueued on the caller's stream
+  CUDA_TRY(cudaEventRecord(s.ev_u1, s.sm));
+  CUDA_TRY(cudaStreamWaitEvent(s.sp, s.ev_u1, 0));
+  return s.run();
+}

@@ -40,6 +40,20 @@ def max_over_ranks(value):
     return float(t.item())
 
 
+def potrf_1d_blocks(n, nb, ranks, rank):
+    """Global block-column indices held by `rank` under cap_potrf_1d's boustrophedon deal, in local order:
+    block j belongs to round r = j // P and to rank (j % P if r is even else P-1 - j % P), where it is local block r."""
+    nblk = -(-n // nb)
+    out = []
+    r = 0
+    while True:
+        j = r * ranks + (ranks - 1 - rank if r & 1 else rank)
+        if j >= nblk:
+            return out
+        out.append(j)
+        r += 1
+
+
 class Comm:
     """NCCL communicator owned by the C-ABI library (cap_comm_t), bootstrapped through torch.distributed."""
 

@@ -100,6 +100,18 @@ class Engine:
     def set_block_sizes(self, potrf_nb=1024, trsm_nb=512):
         _lib.check(self.lib.cap_set_block_sizes(self.h, int(potrf_nb), int(trsm_nb)), "cap_set_block_sizes")
 
+    def set_lookahead(self, reserve_sms=16):
+        _lib.check(self.lib.cap_set_lookahead(self.h, int(reserve_sms)), "cap_set_lookahead")
+
+    def set_potrf_schedule(self, schedule):
+        """0 = right-looking with look-ahead (cap_potrf_1d on one rank), 1 = recursive potrf / trsm / syrk."""
+        _lib.check(self.lib.cap_set_potrf_schedule(self.h, int(schedule)), "cap_set_potrf_schedule")
+
+    def potrf_1d(self, A_loc, N, nb, comm=None):
+        """Look-ahead Cholesky of the global N x N matrix whose block columns (capital_b200.dist.potrf_1d_blocks) this rank
+        holds side by side in A_loc (N x ncols_loc, column-major); comm = the raw cap_comm_t or None."""
+        _lib.check(self.lib.cap_potrf_1d(self.h, comm, N, nb, A_loc.data_ptr(), _ld(A_loc)), "cap_potrf_1d")
+
     # ---- lapack::engine -----------------------------------------------------------------------
     def _potrf(self, A, n, uplo="U"):
         _lib.check(self.lib.cap_dpotrf(self.h, _c(uplo), n, A.data_ptr(), _ld(A)), "cap_dpotrf")

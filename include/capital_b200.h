@@ -143,6 +143,23 @@ int cap_summa_syrk(cap_handle_t h, cap_grid_t grid, char uplo, char trans, int64
 int cap_cholinv_factor(cap_handle_t h, cap_grid_t grid, int64_t n_loc, double* A, int64_t lda, double* Rinv, int64_t ldri,
                        int complete_inv, int split, int64_t bc_global);
 
+/* ---- Cholesky with look-ahead, one GPU or block columns dealt 1-D over the ranks of comm -----------------------------
+ * A = R^T R (upper) of a global N x N SPD matrix, N^3/3 flops: what lapack::engine::_potrf computes
+ * (src/lapack/interface.hpp:31-43), as a right-looking blocked schedule whose diagonal-block work (factor + inverse of
+ * an nb x nb block, broadcast, row-panel solve, all-gather) runs on a second stream WHILE the previous panel's
+ * trailing update occupies the tensor pipes (BASELINE.json north_star allows a 1D grid for the Cholesky target).
+ * Layout: block columns of width nb (multiple of 128); block j -> round r = j / P, rank (r even ? j % P : P-1 - j % P),
+ * local block r; a rank's blocks sit side by side in one column-major N x ncols_loc array (lda >= N).  Only the upper
+ * triangle of the global matrix is read; on exit it holds R, everything below the diagonal is untouched.
+ * comm == NULL: one rank (this is what cap_dpotrf runs when its schedule is 0). */
+int cap_potrf_1d(cap_handle_t h, cap_comm_t comm, int64_t N, int nb, double* A_loc, int64_t lda);
+int cap_potrf_1d_layout(int64_t N, int nb, int nranks, int rank, int64_t* ncols_loc, int* nblocks_loc);
+int cap_potrf_1d_block(int64_t j, int nranks, int* owner, int* local_block);
+/* SMs the trailing update leaves to the concurrently running panel (default 16; 0 = no reservation) */
+int cap_set_lookahead(cap_handle_t h, int reserve_sms);
+/* cap_dpotrf on more than one potrf_nb block: 0 = cap_potrf_1d on one rank, 1 = recursive potrf / trsm / syrk */
+int cap_set_potrf_schedule(cap_handle_t h, int schedule);
+
 /* ---- algorithm entry points (device-resident; src/alg/...) ----------------------------------- */
 /* qr::cacqr::factor, 1D (cacqr.hpp:219-248 -> invoke_1d :174-193).  A is the local m_loc x n row block
  * (untouched), Q the output block, R the n x n upper factor (full layout, strict lower zero).

@@ -122,3 +122,57 @@ def test_trtri_batched_leaves_vs_numpy(engine, uplo, n):
     assert relerr(keep(out), np.linalg.inv(tri)) <= TOL_FACTOR
     other = np.tril(out, -1) if uplo == "U" else np.triu(out, 1)
     assert np.array_equal(other, np.tril(stored, -1) if uplo == "U" else np.triu(stored, 1))
+
+
+@pytest.mark.parametrize("n,nb,reserve", [(100, 128, 16), (640, 128, 16), (1000, 256, 0), (1300, 256, 16), (2500, 512, 16), (4096, 1024, 8)])
+def test_potrf_lookahead_one_rank_vs_numpy(blocks, n, nb, reserve):
+    """cap_potrf_1d on one rank = cap_dpotrf with schedule 0: right-looking, panel(j+1) beside the trailing update of j."""
+    from capital_b200.engine import colmajor
+    eng = blocks
+    eng.set_block_sizes(nb, 512); eng.set_lookahead(reserve); eng.set_potrf_schedule(0)
+    try:
+        A = colmajor(n, n); eng.fill_symmetric(A, 0, 0, 1, 1, n, True)
+        a_np = orc.symmetric_global(n)
+        R = np.linalg.cholesky(a_np).T
+        for _ in range(3):                                                   # repeated: the double-buffered panels and events are reused
+            eng.fill_symmetric(A, 0, 0, 1, 1, n, True)
+            eng.reset_info(); eng._potrf(A, n, "U")
+            out = host(A)
+            assert eng.info() == 0
+            assert relerr(np.triu(out), R) <= TOL_FACTOR
+            assert np.array_equal(np.tril(out, -1), np.tril(a_np, -1))
+        assert orc.cholesky_residual(a_np, np.triu(out)) <= TOL_RESIDUAL_PER_N * n
+    finally:
+        eng.set_potrf_schedule(1); eng.set_lookahead(16)
+
+
+def test_potrf_lookahead_info(blocks):
+    eng = blocks
+    eng.set_block_sizes(256, 512); eng.set_potrf_schedule(0)
+    try:
+        n = 900
+        rng = np.random.default_rng(4)
+        p = rng.random((2 * n, n)) - 0.5
+        s = p.T @ p + 0.5 * np.eye(n)
+        A = dev(s); eng.reset_info(); eng._potrf(A, n, "U")
+        assert eng.info() == 0 and relerr(np.triu(host(A)), np.linalg.cholesky(s).T) <= 1e-10
+        s[600, 600] = -1.0
+        A = dev(s); eng.reset_info(); eng._potrf(A, n, "U")
+        assert eng.info() == 601
+        eng.reset_info()
+    finally:
+        eng.set_potrf_schedule(1)
+
+
+@pytest.mark.parametrize("world,n,nb", [(2, 1500, 256), (2, 4096, 512)])
+def test_potrf_1d_two_gpus(world, n, nb):
+    import os
+    import subprocess
+    import sys
+    from conftest import ROOT
+    if torch.cuda.device_count() < world:
+        pytest.skip("needs %d GPUs" % world)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=%d" % world, "--master-addr", "127.0.0.1",
+           "--master-port", "29561", os.path.join(ROOT, "tools", "potrf1d_check.py"), str(n), str(nb)]
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0 and out.stdout.count("OK") == world, out.stdout[-2000:] + out.stderr[-2000:]

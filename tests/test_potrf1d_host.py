@@ -1,0 +1,187 @@
+"""Host-side logic of cap_potrf_1d (csrc/potrf_1d.cuh) on CPU: the boustrophedon block-column deal exported by the
+C ABI agrees with the Python helper, balances the triangular work, and a numpy walk-through of the schedule that
+uses exactly the index formulas of the CUDA host code (owner / upto / cols_right / run detection / the gathered-panel
+ordering) reproduces LAPACK's Cholesky factor for every rank count and ragged size."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from capital_b200 import _lib, dist as cdist
+
+
+def c_layout(n, nb, ranks, rank):
+    lib = _lib.load()
+    cols, blocks = C.c_int64(), C.c_int()
+    _lib.check(lib.cap_potrf_1d_layout(n, nb, ranks, rank, C.byref(cols), C.byref(blocks)), "layout")
+    return cols.value, blocks.value
+
+
+def c_block(j, ranks):
+    lib = _lib.load()
+    own, loc = C.c_int(), C.c_int()
+    _lib.check(lib.cap_potrf_1d_block(j, ranks, C.byref(own), C.byref(loc)), "block")
+    return own.value, loc.value
+
+
+@pytest.mark.parametrize("n,nb,ranks", [(1, 128, 1), (1000, 128, 3), (4096, 256, 8), (32768, 1024, 8), (5000, 512, 4), (300, 128, 8)])
+def test_layout_matches_python_helper(n, nb, ranks):
+    nblk = -(-n // nb)
+    seen = {}
+    for p in range(ranks):
+        mine = cdist.potrf_1d_blocks(n, nb, ranks, p)
+        cols, blocks = c_layout(n, nb, ranks, p)
+        assert blocks == len(mine)
+        assert cols == sum(min(nb, n - j * nb) for j in mine)
+        assert mine == sorted(mine)                                          # local order = global order
+        for r, j in enumerate(mine):
+            assert c_block(j, ranks) == (p, r)
+            seen[j] = p
+    assert sorted(seen) == list(range(nblk))                                 # every block has exactly one owner
+
+
+def test_layout_balances_the_upper_triangle():
+    """Work of block column j in a right-looking upper Cholesky ~ (j+1)^2 / 2 block products (summed over panels)."""
+    n, nb, ranks = 32768, 512, 8
+    work = [sum((j + 1) ** 2 for j in cdist.potrf_1d_blocks(n, nb, ranks, p)) for p in range(ranks)]
+    assert max(work) / (sum(work) / ranks) < 1.06
+    plain = [sum((j + 1) ** 2 for j in range(p, n // nb, ranks)) for p in range(ranks)]
+    assert max(plain) / (sum(plain) / ranks) > 1.15                          # what the plain cyclic deal would cost
+
+
+class Layout:
+    """The formulas of struct Layout1D, verbatim."""
+
+    def __init__(self, P, nb, N):
+        self.P, self.nb, self.N, self.nblk = P, nb, N, -(-N // nb)
+
+    def owner(self, j):
+        r, pos = divmod(j, self.P)
+        return self.P - 1 - pos if r & 1 else pos
+
+    def global_block(self, r, p):
+        return r * self.P + (self.P - 1 - p if r & 1 else p)
+
+    def width(self, j):
+        return min(self.nb, self.N - j * self.nb)
+
+    def nloc(self, p):
+        n = 0
+        while self.global_block(n, p) < self.nblk:
+            n += 1
+        return n
+
+    def upto(self, p, j):
+        rj, pos = divmod(j, self.P)
+        return rj + (1 if (self.P - 1 - p if rj & 1 else p) <= pos else 0)
+
+    def cols(self, p):
+        n = self.nloc(p)
+        return 0 if n == 0 else (n - 1) * self.nb + self.width(self.global_block(n - 1, p))
+
+    def cols_right(self, p, j):
+        return max(0, self.cols(p) - min(self.upto(p, j), self.nloc(p)) * self.nb)
+
+
+def walk(a, nb, P):
+    """numpy walk-through of Potrf1D::run over P virtual ranks; returns the assembled upper factor."""
+    N = a.shape[0]
+    L = Layout(P, nb, N)
+    loc = [np.concatenate([a[:, j * nb:j * nb + L.width(j)] for j in cdist.potrf_1d_blocks(N, nb, P, p)] or [np.zeros((N, 0))], axis=1).copy()
+           for p in range(P)]
+    S = [None] * P
+    Rrow = None
+
+    def panel(j):
+        nonlocal Rrow
+        own, w = L.owner(j), L.width(j)
+        blk = loc[own][j * nb:j * nb + w, (j // P) * nb:(j // P) * nb + w]
+        r = np.linalg.cholesky(np.triu(blk) + np.triu(blk, 1).T).T
+        blk[np.triu_indices(w)] = r[np.triu_indices(w)]
+        if j == L.nblk - 1:
+            return
+        x = np.linalg.inv(r)                                                  # broadcast
+        maxcl = max(L.cols_right(p, j) for p in range(P))
+        gath = np.full((P, nb * maxcl), np.nan)
+        for p in range(P):
+            r0, ncl = min(L.upto(p, j), L.nloc(p)), L.cols_right(p, j)
+            if ncl > 0:
+                bp = loc[p][j * nb:(j + 1) * nb, r0 * nb:r0 * nb + ncl]
+                bp[...] = x.T @ bp
+                S[p] = bp.copy()
+                gath[p, :nb * ncl] = S[p].T.reshape(-1)                       # column-major nb x ncl
+            else:
+                S[p] = np.zeros((nb, 0))
+        # assemble_row_panel_kernel: block l > j comes from rank owner(l), local position l // P - upto(owner, j)
+        parts = []
+        for l in range(j + 1, L.nblk):
+            own_l, w_l = L.owner(l), L.width(l)
+            off = (l // P - L.upto(own_l, j)) * nb * nb
+            parts.append(gath[own_l, off:off + nb * w_l].reshape(w_l, nb).T)
+        Rrow = np.concatenate(parts, axis=1)
+        assert not np.isnan(Rrow).any()
+
+    def update_next_row(j, p):
+        k, wk = j + 1, L.width(j + 1)
+        r0 = min(L.upto(p, j), L.nloc(p))
+        rr = r0
+        if p == L.owner(k):
+            sk = S[p][:, (k // P - r0) * nb:(k // P - r0) * nb + wk]
+            d = loc[p][k * nb:k * nb + wk, (k // P) * nb:(k // P) * nb + wk]
+            d[np.triu_indices(wk)] -= (sk.T @ sk)[np.triu_indices(wk)]
+            rr = k // P + 1
+        ncl = L.cols(p) - min(rr, L.nloc(p)) * nb
+        if ncl > 0:
+            loc[p][k * nb:k * nb + wk, rr * nb:rr * nb + ncl] -= Rrow[:, :wk].T @ S[p][:, (rr - r0) * nb:(rr - r0) * nb + ncl]
+
+    def update_rest(j, p):
+        n = L.nloc(p)
+        r0 = min(L.upto(p, j), n)
+        r = r0
+        while r < n and L.global_block(r, p) < j + 2:
+            r += 1
+        while r < n:
+            r_end = r + 1
+            while r_end < n and L.global_block(r_end, p) == L.global_block(r_end - 1, p) + 1:
+                r_end += 1
+            k0 = L.global_block(r, p)
+            wrun = (r_end - 1 - r) * nb + L.width(L.global_block(r_end - 1, p))
+            srun = S[p][:, (r - r0) * nb:(r - r0) * nb + wrun]
+            hrect = (k0 - j - 2) * nb
+            if hrect > 0:
+                loc[p][(j + 2) * nb:(j + 2) * nb + hrect, r * nb:r * nb + wrun] -= Rrow[:, nb:nb + hrect].T @ srun
+            sq = loc[p][k0 * nb:k0 * nb + wrun, r * nb:r * nb + wrun]
+            sq[np.triu_indices(wrun)] -= (srun.T @ srun)[np.triu_indices(wrun)]
+            r = r_end
+
+    panel(0)
+    for j in range(L.nblk - 1):
+        s_prev, r_prev = [s.copy() for s in S], Rrow.copy()                   # panel(j+1) must not disturb U2(j)'s operands
+        for p in range(P):
+            update_next_row(j, p)
+        s_j, r_j = S[:], Rrow
+        panel(j + 1)
+        s_next, r_next = S[:], Rrow
+        if j + 2 < L.nblk:
+            S[:], Rrow = s_prev, r_prev
+            for p in range(P):
+                update_rest(j, p)
+            S[:], Rrow = s_next, r_next
+        del s_j, r_j
+    out = np.zeros((N, N))
+    for p in range(P):
+        for r, j in enumerate(cdist.potrf_1d_blocks(N, nb, P, p)):
+            out[:, j * nb:j * nb + L.width(j)] = loc[p][:, r * nb:r * nb + L.width(j)]
+    return out
+
+
+@pytest.mark.parametrize("P", [1, 2, 3, 4, 8])
+@pytest.mark.parametrize("n,nb", [(8, 8), (40, 8), (67, 8), (130, 8), (96, 16)])
+def test_schedule_walkthrough_matches_lapack(P, n, nb):
+    rng = np.random.default_rng(n + P)
+    m = rng.random((n, n)) - 0.5
+    a = m @ m.T + n * np.eye(n)
+    out = walk(a.copy(), nb, P)
+    r = np.linalg.cholesky(a).T
+    assert np.allclose(np.triu(out), r, rtol=1e-11, atol=1e-12)
+    assert np.array_equal(np.tril(out, -1), np.tril(a, -1))                  # nothing below the diagonal is written
