@@ -19,7 +19,7 @@ _SIGS = {
     "cap_dtrmm": [_ptr, _chr, _chr, _chr, _chr, _i64, _i64, _dbl, _ptr, _i64, _ptr, _i64],
     "cap_dtrmm_oop": [_ptr, _chr, _chr, _chr, _chr, _i64, _i64, _dbl, _ptr, _i64, _ptr, _i64, _ptr, _i64],
     "cap_dtrsm": [_ptr, _chr, _chr, _chr, _chr, _i64, _i64, _dbl, _ptr, _i64, _ptr, _i64],
-    "cap_set_block_sizes": [_ptr, _int, _int], "cap_set_lookahead": [_ptr, _int], "cap_set_potrf_schedule": [_ptr, _int],
+    "cap_set_block_sizes": [_ptr, _int, _int], "cap_set_lookahead": [_ptr, _int, _int], "cap_set_potrf_schedule": [_ptr, _int],
     "cap_potrf_1d": [_ptr, _ptr, _i64, _int, _ptr, _i64],
     "cap_potrf_1d_layout": [_i64, _int, _int, _int, C.POINTER(_i64), C.POINTER(_int)],
     "cap_potrf_1d_block": [_i64, _int, C.POINTER(_int), C.POINTER(_int)],

@@ -99,8 +99,10 @@ int cap_destroy(cap_handle_t h) {
   if (h->ev_b) cudaEventDestroy(h->ev_b);
   if (h->panel_stream) {
     cudaStreamDestroy(h->panel_stream);
-    cudaEventDestroy(h->ev_panel[0]); cudaEventDestroy(h->ev_panel[1]); cudaEventDestroy(h->ev_u1);
+    cudaStreamDestroy(h->gather_stream);
+    for (cudaEvent_t e : {h->ev_panel[0], h->ev_panel[1], h->ev_u1, h->ev_trmm, h->ev_gath[0], h->ev_gath[1], h->ev_u2}) cudaEventDestroy(e);
   }
+  if (h->dup_comm) cap_comm_destroy(h->dup_comm);
   cudaStreamDestroy(h->own_stream);
   cudaStreamDestroy(h->copy_stream);
   delete h;

@@ -24,6 +24,11 @@ struct cap_handle_s {
   cudaEvent_t ev_a = nullptr, ev_b = nullptr;
   cudaStream_t panel_stream = nullptr; // look-ahead Cholesky: high-priority stream of the panel operations
   cudaEvent_t ev_panel[2] = {nullptr, nullptr}, ev_u1 = nullptr;
+  cudaStream_t gather_stream = nullptr;  // pipelined look-ahead: stream of the row-panel all-gathers
+  cudaEvent_t ev_trmm = nullptr, ev_gath[2] = {nullptr, nullptr}, ev_u2 = nullptr;
+  struct cap_comm_s* dup_comm = nullptr;     // duplicate of dup_parent for those all-gathers (owned by the handle)
+  struct cap_comm_s* dup_parent = nullptr;
+  int lookahead_pipeline = 1;
   int ws_bank = 0;                    // which split-K workspace slot gemm launches use (1 while launching on the panel stream)
   int lookahead_reserve_sms = 16;     // SMs the trailing update leaves free while a panel runs beside it
   int potrf_schedule = 1;             // cap_dpotrf on more than one block: 0 = right-looking with look-ahead, 1 = recursive

@@ -18,6 +18,14 @@
 // panel(j+1) is enqueued behind U1(j) and runs WHILE U2(j) runs: U2 launches its persistent tile-engine CTAs on
 // num_sms - reserve SMs so that the panel's one-CTA leaf kernels, small products and NCCL kernels have SMs to run on.
 // Buffers of consecutive panels alternate (U2(j) still reads panel j's row while panel(j+1) writes its own).
+//
+// Pipelined variant (cap_set_lookahead's `pipeline` = 1, the default on more than one rank): the all-gather is taken
+// off the critical chain.  The owner of block j+1 needs nothing from the other ranks to update and factor its
+// diagonal block (R_j,j+1 is its own column), so
+//   P: leaf(j) -> bcast X_j -> [wait U1rest(j-1)] R_j,loc -> [owner(j+1): wait U2(j-1); diagonal block -= R_j,j+1^T R_j,j+1] -> leaf(j+1) ...
+//   C: [wait R_j,loc] all-gather(j) on a duplicate communicator -> ordered row panel
+//   M: [wait gather(j)] U1rest(j) = block row j+1 right of the diagonal block -> U2(j)
+// and the chain per panel shrinks from leaf + bcast + solve + all-gather + U1 to leaf + bcast + solve + one block syrk.
 #pragma once
 
 struct Layout1D {
@@ -77,8 +85,10 @@ struct Potrf1D {
   double* A; int64_t lda;
   double *X[2], *S[2], *G[2], *R[2], *Wleaf;   // inverse of the diagonal block, local row panel, gathered, ordered
   int64_t maxcl0;
-  cudaStream_t sm, sp;
+  cudaStream_t sm, sp, sc;
   cudaEvent_t ev_panel[2], ev_u1;
+  cap_comm_t comm2;                             // pipelined variant: duplicate communicator of the all-gathers
+  cudaEvent_t ev_trmm, ev_gath[2], ev_u2;
 
   double* blockptr(int row_block, int local_block) const { return A + (int64_t)row_block * L.nb + (int64_t)local_block * L.nb * lda; }
 
@@ -148,6 +158,89 @@ struct Potrf1D {
     return CAP_OK;
   }
 
+  // ---- pipelined variant: the pieces of panel() and update_next_row() on their own streams ---------------------------
+  int leaf(int j) {                                      // on P, owner only
+    const int nb = L.nb, b = j & 1, w = L.width(j);
+    CUDA_TRY(cudaMemsetAsync(X[b], 0, (size_t)nb * nb * sizeof(double), h->stream));
+    return cholinv_rec(h, blockptr(j, j / L.P), lda, X[b], nb, 0, w, true, j == L.nblk - 1 ? 0 : 1, Wleaf, j * nb);
+  }
+  int row_solve(int j) {                                 // on P: R_j,loc = X_j^T A_j,loc
+    const int nb = L.nb, b = j & 1;
+    const int r0 = std::min(L.upto(me, j), L.nloc(me));
+    const int64_t ncl = L.cols_right(me, j);
+    if (ncl <= 0) return CAP_OK;
+    double* Bp = blockptr(j, r0);
+    CAP_TRY(trmm_impl(h, 'L', 'U', 'T', 'N', nb, ncl, 1.0, X[b], nb, Bp, lda, S[b], nb, true, false));
+    return copy2d(h, Bp, lda, S[b], nb, nb, ncl, 0);
+  }
+  int gather(int j) {                                    // on C
+    const int nb = L.nb, b = j & 1;
+    int64_t maxcl = 0;
+    for (int p = 0; p < L.P; ++p) maxcl = std::max(maxcl, L.cols_right(p, j));
+    CAP_TRY(cap_allgather(h, comm2, S[b], G[b], (int64_t)nb * maxcl));
+    assemble_row_panel_kernel<<<dim3(16, L.nblk - 1 - j), 256, 0, h->stream>>>(R[b], G[b], j, L.P, nb, (int64_t)nb * maxcl, L.N);
+    LAUNCH_CHECK(h);
+    return CAP_OK;
+  }
+  int update_next_diag(int j) {                          // on P, owner(j+1) only: A_kk -= R_jk^T R_jk from its own row-panel block
+    const int nb = L.nb, b = j & 1, k = j + 1;
+    const int r0 = std::min(L.upto(me, j), L.nloc(me));
+    return cap_dsyrk(h, 'U', 'T', L.width(k), nb, -1.0, S[b] + (int64_t)(k / L.P - r0) * nb * nb, nb, 1.0, blockptr(k, k / L.P), lda);
+  }
+  int update_next_row_rest(int j) {                      // on M: block row j+1, columns right of block j+1
+    const int nb = L.nb, b = j & 1, k = j + 1, wk = L.width(k);
+    const int r0 = std::min(L.upto(me, j), L.nloc(me));
+    const int rr = (me == L.owner(k)) ? k / L.P + 1 : r0;
+    const int64_t ncl = L.cols(me) - (int64_t)std::min(rr, L.nloc(me)) * nb;
+    if (ncl <= 0) return CAP_OK;
+    return cap_dgemm(h, 'T', 'N', wk, ncl, nb, -1.0, R[b], nb, S[b] + (int64_t)(rr - r0) * nb * nb, nb, 1.0, blockptr(k, rr), lda);
+  }
+
+  int run_pipelined() {
+    const int nblk = L.nblk;
+    auto panel_front = [&](int j) -> int {               // leaf (owner) -> bcast -> [row j complete] solve -> [owner(j+1)] next diagonal block
+      StreamScope scope(h, sp, 1);
+      if (me == L.owner(j)) CAP_TRY(leaf(j));
+      if (j == nblk - 1) return CAP_OK;
+      CAP_TRY(cap_bcast(h, comm, X[j & 1], (int64_t)L.nb * L.nb, L.owner(j)));
+      if (j > 0) CUDA_TRY(cudaStreamWaitEvent(sp, ev_u1, 0));          // U1rest(j-1) and every U2 before it
+      CAP_TRY(row_solve(j));
+      CUDA_TRY(cudaEventRecord(ev_trmm, sp));
+      if (me == L.owner(j + 1)) {
+        if (j > 0) CUDA_TRY(cudaStreamWaitEvent(sp, ev_u2, 0));        // U2(j-1): the last earlier update of block (j+1, j+1)
+        CAP_TRY(update_next_diag(j));
+      }
+      return CAP_OK;
+    };
+    CUDA_TRY(cudaEventRecord(ev_u2, sm));                 // so that a wait on it is never a wait on a stale record of an earlier call
+    CAP_TRY(panel_front(0));
+    for (int j = 0; j + 1 < nblk; ++j) {
+      const int b = j & 1;
+      if (L.P > 1) {
+        StreamScope scope(h, sc, 1);
+        CUDA_TRY(cudaStreamWaitEvent(sc, ev_trmm, 0));
+        CAP_TRY(gather(j));
+        CUDA_TRY(cudaEventRecord(ev_gath[b], sc));
+        CUDA_TRY(cudaStreamWaitEvent(sm, ev_gath[b], 0));
+      } else {
+        CUDA_TRY(cudaStreamWaitEvent(sm, ev_trmm, 0));
+      }
+      CAP_TRY(update_next_row_rest(j));
+      CUDA_TRY(cudaEventRecord(ev_u1, sm));
+      if (j + 2 < nblk) {
+        SmCapScope cap(h, h->lookahead_reserve_sms > 0 ? h->num_sms - h->lookahead_reserve_sms : 0);
+        CAP_TRY(update_rest(j));
+        CUDA_TRY(cudaEventRecord(ev_u2, sm));
+      }
+      CAP_TRY(panel_front(j + 1));
+    }
+    // join: everything on P (the last leaf) and C is ordered before whatever follows on the caller's stream
+    CUDA_TRY(cudaEventRecord(ev_panel[0], sp));
+    CUDA_TRY(cudaStreamWaitEvent(sm, ev_panel[0], 0));
+    if (L.P > 1) { CUDA_TRY(cudaEventRecord(ev_panel[1], sc)); CUDA_TRY(cudaStreamWaitEvent(sm, ev_panel[1], 0)); }
+    return CAP_OK;
+  }
+
   int run() {
     const int nblk = L.nblk;
     CAP_TRY(panel(0));
@@ -169,9 +262,11 @@ struct Potrf1D {
   }
 };
 
-int cap_set_lookahead(cap_handle_t h, int reserve_sms) {
+int cap_set_lookahead(cap_handle_t h, int reserve_sms, int pipeline) {
   if (reserve_sms < 0 || reserve_sms >= h->num_sms) return cap_fail(CAP_ERR_ARG, "cap_set_lookahead", "reserve must be in [0, #SMs)");
+  if (pipeline < 0 || pipeline > 1) return cap_fail(CAP_ERR_ARG, "cap_set_lookahead", "pipeline: 0 = two streams, 1 = all-gather on its own stream and communicator");
   h->lookahead_reserve_sms = reserve_sms;
+  h->lookahead_pipeline = pipeline;
   return CAP_OK;
 }
 
@@ -202,12 +297,22 @@ int cap_potrf_1d(cap_handle_t h, cap_comm_t comm, int64_t N, int nb, double* A_l
     int lo = 0, hi = 0;
     CUDA_TRY(cudaDeviceGetStreamPriorityRange(&lo, &hi));
     CUDA_TRY(cudaStreamCreateWithPriority(&h->panel_stream, cudaStreamNonBlocking, hi));
-    for (cudaEvent_t* e : {&h->ev_panel[0], &h->ev_panel[1], &h->ev_u1}) CUDA_TRY(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+    CUDA_TRY(cudaStreamCreateWithPriority(&h->gather_stream, cudaStreamNonBlocking, hi));
+    for (cudaEvent_t* e : {&h->ev_panel[0], &h->ev_panel[1], &h->ev_u1, &h->ev_trmm, &h->ev_gath[0], &h->ev_gath[1], &h->ev_u2})
+      CUDA_TRY(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
   }
-  s.sm = h->stream; s.sp = h->panel_stream;
+  const bool pipelined = h->lookahead_pipeline == 1;
+  if (pipelined && P > 1 && h->dup_parent != comm) {     // duplicate communicator for the all-gathers, made once per parent
+    if (h->dup_comm) { cap_comm_destroy(h->dup_comm); h->dup_comm = nullptr; h->dup_parent = nullptr; }
+    CAP_TRY(cap_comm_split(comm, 0, me, &h->dup_comm));
+    h->dup_parent = comm;
+  }
+  s.sm = h->stream; s.sp = h->panel_stream; s.sc = h->gather_stream; s.comm2 = h->dup_comm;
   s.ev_panel[0] = h->ev_panel[0]; s.ev_panel[1] = h->ev_panel[1]; s.ev_u1 = h->ev_u1;
+  s.ev_trmm = h->ev_trmm; s.ev_gath[0] = h->ev_gath[0]; s.ev_gath[1] = h->ev_gath[1]; s.ev_u2 = h->ev_u2;
   // the panel stream starts behind everything already enqueued on the caller's stream
   CUDA_TRY(cudaEventRecord(s.ev_u1, s.sm));
   CUDA_TRY(cudaStreamWaitEvent(s.sp, s.ev_u1, 0));
-  return s.run();
+  CUDA_TRY(cudaStreamWaitEvent(s.sc, s.ev_u1, 0));
+  return pipelined ? s.run_pipelined() : s.run();
 }

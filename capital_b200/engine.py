@@ -100,8 +100,8 @@ class Engine:
     def set_block_sizes(self, potrf_nb=1024, trsm_nb=512):
         _lib.check(self.lib.cap_set_block_sizes(self.h, int(potrf_nb), int(trsm_nb)), "cap_set_block_sizes")
 
-    def set_lookahead(self, reserve_sms=16):
-        _lib.check(self.lib.cap_set_lookahead(self.h, int(reserve_sms)), "cap_set_lookahead")
+    def set_lookahead(self, reserve_sms=16, pipeline=1):
+        _lib.check(self.lib.cap_set_lookahead(self.h, int(reserve_sms), int(pipeline)), "cap_set_lookahead")
 
     def set_potrf_schedule(self, schedule):
         """0 = right-looking with look-ahead (cap_potrf_1d on one rank), 1 = recursive potrf / trsm / syrk."""

@@ -155,8 +155,11 @@ int cap_cholinv_factor(cap_handle_t h, cap_grid_t grid, int64_t n_loc, double* A
 int cap_potrf_1d(cap_handle_t h, cap_comm_t comm, int64_t N, int nb, double* A_loc, int64_t lda);
 int cap_potrf_1d_layout(int64_t N, int nb, int nranks, int rank, int64_t* ncols_loc, int* nblocks_loc);
 int cap_potrf_1d_block(int64_t j, int nranks, int* owner, int* local_block);
-/* SMs the trailing update leaves to the concurrently running panel (default 16; 0 = no reservation) */
-int cap_set_lookahead(cap_handle_t h, int reserve_sms);
+/* reserve_sms: SMs the trailing update leaves to the concurrently running panel (default 16; 0 = no reservation).
+ * pipeline: 1 (default) = the row-panel all-gather runs on its own stream and a duplicate communicator, off the
+ * diagonal-block chain; 0 = panel operations and all-gather in one stream.  NOTE: with pipeline = 1 the handle keeps
+ * a duplicate of comm; destroy the handle before the communicator it was used with. */
+int cap_set_lookahead(cap_handle_t h, int reserve_sms, int pipeline);
 /* cap_dpotrf on more than one potrf_nb block: 0 = cap_potrf_1d on one rank, 1 = recursive potrf / trsm / syrk */
 int cap_set_potrf_schedule(cap_handle_t h, int schedule);
 

@@ -124,12 +124,13 @@ def test_trtri_batched_leaves_vs_numpy(engine, uplo, n):
     assert np.array_equal(other, np.tril(stored, -1) if uplo == "U" else np.triu(stored, 1))
 
 
+@pytest.mark.parametrize("pipeline", [0, 1])
 @pytest.mark.parametrize("n,nb,reserve", [(100, 128, 16), (640, 128, 16), (1000, 256, 0), (1300, 256, 16), (2500, 512, 16), (4096, 1024, 8)])
-def test_potrf_lookahead_one_rank_vs_numpy(blocks, n, nb, reserve):
+def test_potrf_lookahead_one_rank_vs_numpy(blocks, n, nb, reserve, pipeline):
     """cap_potrf_1d on one rank = cap_dpotrf with schedule 0: right-looking, panel(j+1) beside the trailing update of j."""
     from capital_b200.engine import colmajor
     eng = blocks
-    eng.set_block_sizes(nb, 512); eng.set_lookahead(reserve); eng.set_potrf_schedule(0)
+    eng.set_block_sizes(nb, 512); eng.set_lookahead(reserve, pipeline); eng.set_potrf_schedule(0)
     try:
         A = colmajor(n, n); eng.fill_symmetric(A, 0, 0, 1, 1, n, True)
         a_np = orc.symmetric_global(n)
@@ -143,7 +144,7 @@ def test_potrf_lookahead_one_rank_vs_numpy(blocks, n, nb, reserve):
             assert np.array_equal(np.tril(out, -1), np.tril(a_np, -1))
         assert orc.cholesky_residual(a_np, np.triu(out)) <= TOL_RESIDUAL_PER_N * n
     finally:
-        eng.set_potrf_schedule(1); eng.set_lookahead(16)
+        eng.set_potrf_schedule(1); eng.set_lookahead(16, 1)
 
 
 def test_potrf_lookahead_info(blocks):
@@ -164,8 +165,8 @@ def test_potrf_lookahead_info(blocks):
         eng.set_potrf_schedule(1)
 
 
-@pytest.mark.parametrize("world,n,nb", [(2, 1500, 256), (2, 4096, 512)])
-def test_potrf_1d_two_gpus(world, n, nb):
+@pytest.mark.parametrize("world,n,nb,pipeline", [(2, 1500, 256, 1), (2, 4096, 512, 0), (4, 3000, 256, 1), (8, 4096, 256, 1)])
+def test_potrf_1d_multi_gpu(world, n, nb, pipeline):
     import os
     import subprocess
     import sys
@@ -173,6 +174,6 @@ def test_potrf_1d_two_gpus(world, n, nb):
     if torch.cuda.device_count() < world:
         pytest.skip("needs %d GPUs" % world)
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=%d" % world, "--master-addr", "127.0.0.1",
-           "--master-port", "29561", os.path.join(ROOT, "tools", "potrf1d_check.py"), str(n), str(nb)]
+           "--master-port", "29561", os.path.join(ROOT, "tools", "potrf1d_check.py"), str(n), str(nb), "--pipeline", str(pipeline)]
     out = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert out.returncode == 0 and out.stdout.count("OK") == world, out.stdout[-2000:] + out.stderr[-2000:]
