@@ -563,8 +563,8 @@ int cap_set_potrf_schedule(cap_handle_t h, int schedule) {
 }
 
 int cap_set_block_sizes(cap_handle_t h, int potrf_nb, int trsm_nb) {
-  if (potrf_nb < BASE_NB || potrf_nb % BASE_NB || trsm_nb < BASE_NB || trsm_nb % BASE_NB)
-    return cap_fail(CAP_ERR_ARG, "cap_set_block_sizes", "block sizes must be positive multiples of 128");
+  if (potrf_nb < 0 || potrf_nb % BASE_NB || trsm_nb < BASE_NB || trsm_nb % BASE_NB)
+    return cap_fail(CAP_ERR_ARG, "cap_set_block_sizes", "block sizes must be positive multiples of 128 (potrf_nb: 0 = chosen by size)");
   h->potrf_nb = potrf_nb; h->trsm_nb = trsm_nb;
   return CAP_OK;
 }
@@ -619,7 +619,8 @@ static int potrf_rec(const PotrfCtx& c, int off, int len) {
 int cap_dpotrf(cap_handle_t h, char uplo, int n, double* A, int lda) {
   if (!is_u(uplo)) return cap_fail(CAP_ERR_UNSUPPORTED, "cap_dpotrf", "only uplo='U' (the reference asserts dir=='U', cholinv.hpp:9)");
   if (n <= 0) return n == 0 ? CAP_OK : cap_fail(CAP_ERR_ARG, "cap_dpotrf", "bad dimension");
-  const int nb = h->potrf_nb;
+  // block size: measured on B200 (tools/factor_probe.py, tools/potrf1d_check.py) 1024 is best at n = 8192, 2048 at 16384
+  const int nb = h->potrf_nb > 0 ? h->potrf_nb : std::min(2048, std::max(512, (n / 8 + BASE_NB - 1) / BASE_NB * BASE_NB));
   if (n <= nb) {   // one block: the cholinv recursion without its top-level inverse completion
     double* X;
     CAP_TRY(cap_workspace(h, CAP_WS_FACTOR, (size_t)n * n * sizeof(double), &X));

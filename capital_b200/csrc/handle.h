@@ -28,16 +28,16 @@ struct cap_handle_s {
   cudaEvent_t ev_trmm = nullptr, ev_gath[2] = {nullptr, nullptr}, ev_u2 = nullptr;
   struct cap_comm_s* dup_comm = nullptr;     // duplicate of dup_parent for those all-gathers (owned by the handle)
   struct cap_comm_s* dup_parent = nullptr;
-  int lookahead_pipeline = 1;
+  int lookahead_pipeline = -1;        // -1 = by rank count (measured: 1 on one rank, 0 on several), 0 / 1 forced
   int ws_bank = 0;                    // which split-K workspace slot gemm launches use (1 while launching on the panel stream)
   int lookahead_reserve_sms = 16;     // SMs the trailing update leaves free while a panel runs beside it
-  int potrf_schedule = 1;             // cap_dpotrf on more than one block: 0 = right-looking with look-ahead, 1 = recursive
+  int potrf_schedule = 0;             // cap_dpotrf on more than one block: 0 = right-looking with look-ahead, 1 = recursive
   int* info_dev = nullptr;
   long long launches = 0;
   void* encode_tiled = nullptr;       // cuTensorMapEncodeTiled
   size_t host_chunk_bytes = (size_t)1 << 30;   // row-chunk size of the pipelined host entry points
   int engine = 0;                     // 0 = auto (TMA engine when alignment allows), 1 = cp.async engine only
-  int potrf_nb = 1024;                // cap_dpotrf: largest diagonal block factored + inverted by the cholinv recursion
+  int potrf_nb = 0;                   // cap_dpotrf: largest diagonal block factored + inverted by the cholinv recursion (0 = by size)
   int trsm_nb = 512;                  // cap_dtrsm: largest diagonal block applied through its explicit inverse
   cap_ws_slot ws[CAP_WS_SLOTS];
 };

@@ -19,7 +19,7 @@
 // num_sms - reserve SMs so that the panel's one-CTA leaf kernels, small products and NCCL kernels have SMs to run on.
 // Buffers of consecutive panels alternate (U2(j) still reads panel j's row while panel(j+1) writes its own).
 //
-// Pipelined variant (cap_set_lookahead's `pipeline` = 1, the default on more than one rank): the all-gather is taken
+// Pipelined variant (cap_set_lookahead's `pipeline` = 1; the default on ONE rank only, see cap_potrf_1d): the all-gather is taken
 // off the critical chain.  The owner of block j+1 needs nothing from the other ranks to update and factor its
 // diagonal block (R_j,j+1 is its own column), so
 //   P: leaf(j) -> bcast X_j -> [wait U1rest(j-1)] R_j,loc -> [owner(j+1): wait U2(j-1); diagonal block -= R_j,j+1^T R_j,j+1] -> leaf(j+1) ...
@@ -264,7 +264,7 @@ struct Potrf1D {
 
 int cap_set_lookahead(cap_handle_t h, int reserve_sms, int pipeline) {
   if (reserve_sms < 0 || reserve_sms >= h->num_sms) return cap_fail(CAP_ERR_ARG, "cap_set_lookahead", "reserve must be in [0, #SMs)");
-  if (pipeline < 0 || pipeline > 1) return cap_fail(CAP_ERR_ARG, "cap_set_lookahead", "pipeline: 0 = two streams, 1 = all-gather on its own stream and communicator");
+  if (pipeline < -1 || pipeline > 1) return cap_fail(CAP_ERR_ARG, "cap_set_lookahead", "pipeline: -1 = by rank count, 0 = two streams, 1 = all-gather on its own stream and communicator");
   h->lookahead_reserve_sms = reserve_sms;
   h->lookahead_pipeline = pipeline;
   return CAP_OK;
@@ -301,7 +301,9 @@ int cap_potrf_1d(cap_handle_t h, cap_comm_t comm, int64_t N, int nb, double* A_l
     for (cudaEvent_t* e : {&h->ev_panel[0], &h->ev_panel[1], &h->ev_u1, &h->ev_trmm, &h->ev_gath[0], &h->ev_gath[1], &h->ev_u2})
       CUDA_TRY(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
   }
-  const bool pipelined = h->lookahead_pipeline == 1;
+  // measured (profiles/r01_potrf1d_*.jsonl): the pipelined order wins on one rank (N = 16384: 53.1 vs 54.0 ms), the
+  // two-stream order on 2 and 8 ranks (N = 32768 on 8: 86.0 vs 97.6 ms)
+  const bool pipelined = h->lookahead_pipeline == 1 || (h->lookahead_pipeline < 0 && P == 1);
   if (pipelined && P > 1 && h->dup_parent != comm) {     // duplicate communicator for the all-gathers, made once per parent
     if (h->dup_comm) { cap_comm_destroy(h->dup_comm); h->dup_comm = nullptr; h->dup_parent = nullptr; }
     CAP_TRY(cap_comm_split(comm, 0, me, &h->dup_comm));

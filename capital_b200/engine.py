@@ -97,10 +97,10 @@ class Engine:
         _lib.check(self.lib.cap_dtrsm(self.h, _c(side), _c(uplo), _c(trans), _c(diag), m, n, alpha, T.data_ptr(), _ld(T),
                                       B.data_ptr(), _ld(B)), "cap_dtrsm")
 
-    def set_block_sizes(self, potrf_nb=1024, trsm_nb=512):
+    def set_block_sizes(self, potrf_nb=0, trsm_nb=512):
         _lib.check(self.lib.cap_set_block_sizes(self.h, int(potrf_nb), int(trsm_nb)), "cap_set_block_sizes")
 
-    def set_lookahead(self, reserve_sms=16, pipeline=1):
+    def set_lookahead(self, reserve_sms=16, pipeline=-1):
         _lib.check(self.lib.cap_set_lookahead(self.h, int(reserve_sms), int(pipeline)), "cap_set_lookahead")
 
     def set_potrf_schedule(self, schedule):

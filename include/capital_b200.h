@@ -70,8 +70,9 @@ int cap_dtrmm_oop(cap_handle_t h, char side, char uplo, char trans, char diag, i
  * tile engine, diagonal blocks of at most trsm_nb applied through their inverses. */
 int cap_dtrsm(cap_handle_t h, char side, char uplo, char trans, char diag, int64_t m, int64_t n, double alpha,
               const double* T, int64_t ldt, double* B, int64_t ldb);
-/* blocking of cap_dpotrf (largest diagonal block factored + inverted by the cholinv recursion, default 1024) and
- * cap_dtrsm (largest diagonal block applied through its inverse, default 512); multiples of 128 */
+/* blocking of cap_dpotrf (largest diagonal block factored + inverted by the cholinv recursion; default 0 = by size:
+ * n/8 clamped to [512, 2048]) and cap_dtrsm (largest diagonal block applied through its inverse, default 512);
+ * multiples of 128 */
 int cap_set_block_sizes(cap_handle_t h, int potrf_nb, int trsm_nb);
 
 /* ---- LAPACK engine (src/lapack/interface.hpp:31-58) ------------------------------------------ */
@@ -156,11 +157,12 @@ int cap_potrf_1d(cap_handle_t h, cap_comm_t comm, int64_t N, int nb, double* A_l
 int cap_potrf_1d_layout(int64_t N, int nb, int nranks, int rank, int64_t* ncols_loc, int* nblocks_loc);
 int cap_potrf_1d_block(int64_t j, int nranks, int* owner, int* local_block);
 /* reserve_sms: SMs the trailing update leaves to the concurrently running panel (default 16; 0 = no reservation).
- * pipeline: 1 (default) = the row-panel all-gather runs on its own stream and a duplicate communicator, off the
- * diagonal-block chain; 0 = panel operations and all-gather in one stream.  NOTE: with pipeline = 1 the handle keeps
- * a duplicate of comm; destroy the handle before the communicator it was used with. */
+ * pipeline: 1 = the row-panel all-gather runs on its own stream and a duplicate communicator, off the diagonal-block
+ * chain; 0 = panel operations and all-gather in one stream; -1 (default) = 1 on one rank, 0 on several (what measured
+ * fastest on 1, 2 and 8 B200).  NOTE: with pipeline = 1 on several ranks the handle keeps a duplicate of comm; destroy
+ * the handle before the communicator it was used with. */
 int cap_set_lookahead(cap_handle_t h, int reserve_sms, int pipeline);
-/* cap_dpotrf on more than one potrf_nb block: 0 = cap_potrf_1d on one rank, 1 = recursive potrf / trsm / syrk */
+/* cap_dpotrf on more than one potrf_nb block: 0 (default) = cap_potrf_1d on one rank, 1 = recursive potrf / trsm / syrk */
 int cap_set_potrf_schedule(cap_handle_t h, int schedule);
 
 /* ---- algorithm entry points (device-resident; src/alg/...) ----------------------------------- */

@@ -35,7 +35,7 @@ def triangular(rng, n, uplo):
 def blocks(engine):
     """Restore the default blocking after a test that shrinks it."""
     yield engine
-    engine.set_block_sizes(1024, 512)
+    engine.set_block_sizes(0, 512); engine.set_potrf_schedule(0); engine.set_lookahead(16, -1)
 
 
 @pytest.mark.parametrize("side", ["L", "R"])
@@ -82,7 +82,7 @@ def test_potrf_blocked_vs_numpy(blocks, n, nb):
     """cap_dpotrf on more than one diagonal block: recursive potrf / trsm / triangular syrk."""
     from capital_b200.engine import colmajor
     eng = blocks
-    eng.set_block_sizes(nb, 512)
+    eng.set_block_sizes(nb, 512); eng.set_potrf_schedule(1)
     A = colmajor(n, n); eng.fill_symmetric(A, 0, 0, 1, 1, n, True)
     a_np = orc.symmetric_global(n)
     eng.reset_info(); eng._potrf(A, n, "U")
@@ -97,7 +97,7 @@ def test_potrf_blocked_vs_numpy(blocks, n, nb):
 def test_potrf_blocked_random_spd_and_info(blocks):
     """A less structured SPD matrix (Gram of a random panel), then a non-positive pivot deep inside the second block."""
     eng = blocks
-    eng.set_block_sizes(256, 512)
+    eng.set_block_sizes(256, 512); eng.set_potrf_schedule(1)
     n = 900
     rng = np.random.default_rng(3)
     p = rng.random((2 * n, n)) - 0.5
@@ -144,7 +144,7 @@ def test_potrf_lookahead_one_rank_vs_numpy(blocks, n, nb, reserve, pipeline):
             assert np.array_equal(np.tril(out, -1), np.tril(a_np, -1))
         assert orc.cholesky_residual(a_np, np.triu(out)) <= TOL_RESIDUAL_PER_N * n
     finally:
-        eng.set_potrf_schedule(1); eng.set_lookahead(16, 1)
+        eng.set_potrf_schedule(0); eng.set_lookahead(16, -1)
 
 
 def test_potrf_lookahead_info(blocks):
@@ -162,7 +162,7 @@ def test_potrf_lookahead_info(blocks):
         assert eng.info() == 601
         eng.reset_info()
     finally:
-        eng.set_potrf_schedule(1)
+        eng.set_potrf_schedule(0)
 
 
 @pytest.mark.parametrize("world,n,nb,pipeline", [(2, 1500, 256, 1), (2, 4096, 512, 0), (4, 3000, 256, 1), (8, 4096, 256, 1)])
@@ -177,3 +177,16 @@ def test_potrf_1d_multi_gpu(world, n, nb, pipeline):
            "--master-port", "29561", os.path.join(ROOT, "tools", "potrf1d_check.py"), str(n), str(nb), "--pipeline", str(pipeline)]
     out = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert out.returncode == 0 and out.stdout.count("OK") == world, out.stdout[-2000:] + out.stderr[-2000:]
+
+
+@pytest.mark.parametrize("n", [1500, 3000, 5000])
+def test_potrf_default_schedule_vs_numpy(engine, n):
+    """cap_dpotrf as shipped (block size by n, look-ahead schedule) -- the lapack::engine::_potrf a caller gets."""
+    from capital_b200.engine import colmajor
+    A = colmajor(n, n); engine.fill_symmetric(A, 0, 0, 1, 1, n, True)
+    a_np = orc.symmetric_global(n)
+    engine.reset_info(); engine._potrf(A, n, "U")
+    out = host(A)
+    assert engine.info() == 0
+    assert relerr(np.triu(out), np.linalg.cholesky(a_np).T) <= TOL_FACTOR
+    assert np.array_equal(np.tril(out, -1), np.tril(a_np, -1))

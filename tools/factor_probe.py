@@ -51,14 +51,18 @@ def main():
         t = best_ms(lambda: (W.copy_(S), E.cholinv(W, X, n, False)), args.reps) - t_copy
         report("cholinv ci=0 (reference schedule)", n, t, fl, "(executes 5N^3/12)")
         ref = W.clone()
-        for nb in args.nb:
-            if nb >= n:
-                continue
-            E.set_block_sizes(nb, 512)
-            t = best_ms(lambda: (W.copy_(S), E._potrf(W, n, "U")), args.reps) - t_copy
-            diff = float((torch.triu(W) - torch.triu(ref)).norm() / torch.triu(ref).norm())
-            report("potrf nb=%d" % nb, n, t, fl, "| R vs reference schedule %.1e" % diff)
-        E.set_block_sizes(1024, 512)
+        for sched, name in ((1, "recursive"), (0, "look-ahead")):
+            E.set_potrf_schedule(sched)
+            for nb in args.nb:
+                if nb >= n:
+                    continue
+                E.set_block_sizes(nb, 512)
+                t = best_ms(lambda: (W.copy_(S), E._potrf(W, n, "U")), args.reps) - t_copy
+                diff = float((torch.triu(W) - torch.triu(ref)).norm() / torch.triu(ref).norm())
+                report("potrf %s nb=%d" % (name, nb), n, t, fl, "| R vs reference schedule %.1e" % diff)
+        E.set_block_sizes(0, 512)
+        t = best_ms(lambda: (W.copy_(S), E._potrf(W, n, "U")), args.reps) - t_copy
+        report("potrf as shipped (defaults)", n, t, fl)
         t = best_ms(lambda: (W.copy_(S), E.cholinv(W, X, n, True)), args.reps) - t_copy
         report("cholinv ci=1 (R and R^-1)", n, t, 2 * fl)
         R = torch.triu(ref); del ref
@@ -66,10 +70,10 @@ def main():
         t = best_ms(lambda: (W.copy_(Rm), E._trtri(W, n, "U", "N")), args.reps) - t_copy
         report("trtri (batched leaves)", n, t, fl)
         for nb in (256, 512, 1024):
-            E.set_block_sizes(1024, nb)
+            E.set_block_sizes(0, nb)
             t = best_ms(lambda: (W.copy_(S), E.trsm(Rm, W, n, n, "L", "U", "T", "N", 1.0)), args.reps) - t_copy
             report("trsm L/U/T nb=%d, %d rhs" % (nb, n), n, t, float(n) ** 3)
-        E.set_block_sizes(1024, 512)
+        E.set_block_sizes(0, 512)
         print("info", E.info(), flush=True)
         del S, W, X, Rm
         torch.cuda.empty_cache()
