@@ -80,7 +80,41 @@ struct SmCapScope {
   ~SmCapScope() { h->num_sms = saved; }
 };
 
+// Optional timeline of one factorization (CAPITAL_B200_PROFILE=1: rank 0 prints; =2: every rank): timing events recorded
+// on the three streams at the phase boundaries of every panel, read back after the call has been synchronised.  This is
+// the stand-in for an nsys timeline (not in this image): it shows, per panel, when the diagonal chain and the trailing
+// update started and ended on this rank.  Off by default (no events, no synchronisation).
+struct Timeline1D {
+  struct Stamp { cudaEvent_t ev; int panel; const char* what; };
+  bool on = false;
+  std::vector<Stamp> stamps;
+  void mark(cudaStream_t s, int panel, const char* what) {
+    if (!on) return;
+    cudaEvent_t e;
+    if (cudaEventCreate(&e) != cudaSuccess) { on = false; return; }
+    cudaEventRecord(e, s);
+    stamps.push_back({e, panel, what});
+  }
+  void report(cudaStream_t main_stream, int rank, const Layout1D& L) {
+    if (!on || stamps.empty()) return;
+    cudaStreamSynchronize(main_stream);
+    fprintf(stderr, "[capital_b200 timeline] rank %d  potrf_1d N=%lld nb=%d P=%d  (ms since the first stamp; begin..end per phase)\n", rank, (long long)L.N, L.nb, L.P);
+    int cur = -1;
+    for (size_t i = 0; i + 1 < stamps.size(); i += 2) {       // stamps come in begin/end pairs
+      float t0 = 0, t1 = 0;
+      cudaEventElapsedTime(&t0, stamps[0].ev, stamps[i].ev);
+      cudaEventElapsedTime(&t1, stamps[0].ev, stamps[i + 1].ev);
+      if (stamps[i].panel != cur) { cur = stamps[i].panel; fprintf(stderr, "%s  panel %3d (owner %d):", i ? "\n" : "", cur, L.owner(cur)); }
+      fprintf(stderr, "  %s %.3f..%.3f", stamps[i].what, t0, t1);
+    }
+    fprintf(stderr, "\n");
+    for (auto& st : stamps) cudaEventDestroy(st.ev);
+    stamps.clear();
+  }
+};
+
 struct Potrf1D {
+  Timeline1D tl;
   cap_handle_t h; cap_comm_t comm; Layout1D L; int me;
   double* A; int64_t lda;
   double *X[2], *S[2], *G[2], *R[2], *Wleaf;   // inverse of the diagonal block, local row panel, gathered, ordered
@@ -98,25 +132,33 @@ struct Potrf1D {
     StreamScope scope(h, sp, 1);
     const bool last = (j == L.nblk - 1);
     if (me == own) {
+      tl.mark(sp, j, "leaf");
       CUDA_TRY(cudaMemsetAsync(X[b], 0, (size_t)nb * nb * sizeof(double), h->stream));
       CAP_TRY(cholinv_rec(h, blockptr(j, j / L.P), lda, X[b], nb, 0, w, true, last ? 0 : 1, Wleaf, j * nb));
+      tl.mark(sp, j, "leaf");
     }
     if (last) return CAP_OK;                             // nothing to the right of the last block
+    tl.mark(sp, j, "bcast");
     CAP_TRY(cap_bcast(h, comm, X[b], (int64_t)nb * nb, own));
+    tl.mark(sp, j, "bcast");
     const int r0 = std::min(L.upto(me, j), L.nloc(me));
     const int64_t ncl = L.cols_right(me, j);
     if (ncl > 0) {                                      // R_j,loc = X_j^T A_j,loc, kept in S (the all-gather payload) and in A
       double* Bp = blockptr(j, r0);
+      tl.mark(sp, j, "solve");
       CAP_TRY(trmm_impl(h, 'L', 'U', 'T', 'N', nb, ncl, 1.0, X[b], nb, Bp, lda, S[b], nb, true, false));
       CAP_TRY(copy2d(h, Bp, lda, S[b], nb, nb, ncl, 0));
+      tl.mark(sp, j, "solve");
     }
     if (L.P > 1) {
       int64_t maxcl = 0;
       for (int p = 0; p < L.P; ++p) maxcl = std::max(maxcl, L.cols_right(p, j));
+      tl.mark(sp, j, "gather");
       CAP_TRY(cap_allgather(h, comm, S[b], G[b], (int64_t)nb * maxcl));
       const int nright = L.nblk - 1 - j;
       assemble_row_panel_kernel<<<dim3(16, nright), 256, 0, h->stream>>>(R[b], G[b], j, L.P, nb, (int64_t)nb * maxcl, L.N);
       LAUNCH_CHECK(h);
+      tl.mark(sp, j, "gather");
     }
     return CAP_OK;
   }
@@ -200,15 +242,21 @@ struct Potrf1D {
     const int nblk = L.nblk;
     auto panel_front = [&](int j) -> int {               // leaf (owner) -> bcast -> [row j complete] solve -> [owner(j+1)] next diagonal block
       StreamScope scope(h, sp, 1);
-      if (me == L.owner(j)) CAP_TRY(leaf(j));
+      if (me == L.owner(j)) { tl.mark(sp, j, "leaf"); CAP_TRY(leaf(j)); tl.mark(sp, j, "leaf"); }
       if (j == nblk - 1) return CAP_OK;
+      tl.mark(sp, j, "bcast");
       CAP_TRY(cap_bcast(h, comm, X[j & 1], (int64_t)L.nb * L.nb, L.owner(j)));
+      tl.mark(sp, j, "bcast");
       if (j > 0) CUDA_TRY(cudaStreamWaitEvent(sp, ev_u1, 0));          // U1rest(j-1) and every U2 before it
+      tl.mark(sp, j, "solve");
       CAP_TRY(row_solve(j));
+      tl.mark(sp, j, "solve");
       CUDA_TRY(cudaEventRecord(ev_trmm, sp));
       if (me == L.owner(j + 1)) {
         if (j > 0) CUDA_TRY(cudaStreamWaitEvent(sp, ev_u2, 0));        // U2(j-1): the last earlier update of block (j+1, j+1)
+        tl.mark(sp, j, "U1diag");
         CAP_TRY(update_next_diag(j));
+        tl.mark(sp, j, "U1diag");
       }
       return CAP_OK;
     };
@@ -219,17 +267,23 @@ struct Potrf1D {
       if (L.P > 1) {
         StreamScope scope(h, sc, 1);
         CUDA_TRY(cudaStreamWaitEvent(sc, ev_trmm, 0));
+        tl.mark(sc, j, "gather");
         CAP_TRY(gather(j));
+        tl.mark(sc, j, "gather");
         CUDA_TRY(cudaEventRecord(ev_gath[b], sc));
         CUDA_TRY(cudaStreamWaitEvent(sm, ev_gath[b], 0));
       } else {
         CUDA_TRY(cudaStreamWaitEvent(sm, ev_trmm, 0));
       }
+      tl.mark(sm, j, "U1rest");
       CAP_TRY(update_next_row_rest(j));
+      tl.mark(sm, j, "U1rest");
       CUDA_TRY(cudaEventRecord(ev_u1, sm));
       if (j + 2 < nblk) {
         SmCapScope cap(h, h->lookahead_reserve_sms > 0 ? h->num_sms - h->lookahead_reserve_sms : 0);
+        tl.mark(sm, j, "U2");
         CAP_TRY(update_rest(j));
+        tl.mark(sm, j, "U2");
         CUDA_TRY(cudaEventRecord(ev_u2, sm));
       }
       CAP_TRY(panel_front(j + 1));
@@ -248,14 +302,18 @@ struct Potrf1D {
     for (int j = 0; j < nblk; ++j) {
       CUDA_TRY(cudaStreamWaitEvent(sm, ev_panel[j & 1], 0));
       if (j + 1 >= nblk) break;
+      tl.mark(sm, j, "U1");
       CAP_TRY(update_next_row(j));
+      tl.mark(sm, j, "U1");
       CUDA_TRY(cudaEventRecord(ev_u1, sm));
       CUDA_TRY(cudaStreamWaitEvent(sp, ev_u1, 0));
       CAP_TRY(panel(j + 1));
       CUDA_TRY(cudaEventRecord(ev_panel[(j + 1) & 1], sp));
       if (j + 2 < nblk) {
         SmCapScope cap(h, h->lookahead_reserve_sms > 0 ? h->num_sms - h->lookahead_reserve_sms : 0);
+        tl.mark(sm, j, "U2");
         CAP_TRY(update_rest(j));
+        tl.mark(sm, j, "U2");
       }
     }
     return CAP_OK;
@@ -316,5 +374,9 @@ int cap_potrf_1d(cap_handle_t h, cap_comm_t comm, int64_t N, int nb, double* A_l
   CUDA_TRY(cudaEventRecord(s.ev_u1, s.sm));
   CUDA_TRY(cudaStreamWaitEvent(s.sp, s.ev_u1, 0));
   CUDA_TRY(cudaStreamWaitEvent(s.sc, s.ev_u1, 0));
-  return pipelined ? s.run_pipelined() : s.run();
+  const char* prof = getenv("CAPITAL_B200_PROFILE");
+  s.tl.on = prof && (atoi(prof) >= 2 || (atoi(prof) == 1 && me == 0));
+  const int rc = pipelined ? s.run_pipelined() : s.run();
+  s.tl.report(s.sm, me, s.L);
+  return rc;
 }

@@ -35,6 +35,8 @@ def main():
     ap.add_argument("--time", type=int, default=0)
     ap.add_argument("--reserve", type=int, nargs="+", default=[16])
     ap.add_argument("--no-check", action="store_true")
+    ap.add_argument("--timeline", action="store_true", help="after the timed runs, one more factorization with CAPITAL_B200_PROFILE=2 "
+                    "(per-panel phase timeline of every rank on stderr; warm: no workspace growth inside)")
     ap.add_argument("--json", default=None)
     args = ap.parse_args()
     world, rank, local = int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("RANK", "0")), int(os.environ.get("LOCAL_RANK", "0"))
@@ -119,6 +121,13 @@ def main():
                     if rank == 0:
                         print("potrf_1d N=%d nb=%d on %d GPU(s), pipeline %d, %d SMs reserved: %.3f ms  %.2f TFLOP/s  %.1f %% of %d x %.1f  (rank 0: rel %.1e %s)" % (
                             N, nb, world, pipeline, reserve, t, tf, 100 * tf / (PEAK * world), world, PEAK, worst, "OK" if good else "FAIL"), flush=True)
+        if args.timeline:
+            for _ in range(2):
+                A.copy_(A0); eng.potrf_1d(A, N, nb, cptr)
+            torch.cuda.synchronize()
+            os.environ["CAPITAL_B200_PROFILE"] = "2"
+            A.copy_(A0); eng.potrf_1d(A, N, nb, cptr); torch.cuda.synchronize()
+            os.environ.pop("CAPITAL_B200_PROFILE", None)
         del A, A0
         torch.cuda.empty_cache()
     if rank == 0 and args.json and results:
