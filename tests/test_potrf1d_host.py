@@ -185,3 +185,82 @@ def test_schedule_walkthrough_matches_lapack(P, n, nb):
     r = np.linalg.cholesky(a).T
     assert np.allclose(np.triu(out), r, rtol=1e-11, atol=1e-12)
     assert np.array_equal(np.tril(out, -1), np.tril(a, -1))                  # nothing below the diagonal is written
+
+
+def _gloo_worker(rank, world, port, n, nb, out):
+    """cap_potrf_1d's communication pattern with real collectives over gloo: broadcast of the inverse diagonal block from
+    the owner, all-gather of equally sized (padded) row-panel pieces, ordering by the closed-form owner / position
+    formulas -- one process per rank, each holding only its own block columns."""
+    import os
+    import sys
+    from conftest import ROOT
+    sys.path.insert(0, ROOT)
+    import torch
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    rng = np.random.default_rng(n)
+    m = rng.random((n, n)) - 0.5
+    a = m @ m.T + n * np.eye(n)
+    L = Layout(world, nb, n)
+    mine = cdist.potrf_1d_blocks(n, nb, world, rank)
+    loc = np.concatenate([a[:, j * nb:j * nb + L.width(j)] for j in mine] or [np.zeros((n, 0))], axis=1).copy()
+    for j in range(L.nblk):
+        own, w = L.owner(j), L.width(j)
+        x = torch.zeros((nb, nb), dtype=torch.float64)
+        if rank == own:
+            blk = loc[j * nb:j * nb + w, (j // world) * nb:(j // world) * nb + w]
+            r = np.linalg.cholesky(np.triu(blk) + np.triu(blk, 1).T).T
+            blk[np.triu_indices(w)] = r[np.triu_indices(w)]
+            x[:w, :w] = torch.from_numpy(np.linalg.inv(r))
+        if j == L.nblk - 1:
+            break
+        dist.broadcast(x, own)                                                # cap_bcast of X_j
+        r0, ncl = min(L.upto(rank, j), L.nloc(rank)), L.cols_right(rank, j)
+        maxcl = max(L.cols_right(p, j) for p in range(world))
+        send = torch.full((nb * maxcl,), float("nan"), dtype=torch.float64)     # padding is never read
+        s = np.zeros((nb, 0))
+        if ncl > 0:
+            bp = loc[j * nb:(j + 1) * nb, r0 * nb:r0 * nb + ncl]
+            bp[...] = x.numpy().T @ bp
+            s = bp.copy()
+            send[:nb * ncl] = torch.from_numpy(s.T.reshape(-1).copy())
+        gath = [torch.empty_like(send) for _ in range(world)]
+        dist.all_gather(gath, send)                                            # cap_allgather of the row panel
+        parts = []
+        for l in range(j + 1, L.nblk):
+            own_l, w_l = L.owner(l), L.width(l)
+            off = (l // world - L.upto(own_l, j)) * nb * nb
+            parts.append(gath[own_l][off:off + nb * w_l].numpy().reshape(w_l, nb).T)
+        rrow = np.concatenate(parts, axis=1)
+        assert not np.isnan(rrow).any()
+        for k_loc in range(r0, L.nloc(rank)):                                  # trailing update of the own block columns
+            k = L.global_block(k_loc, rank)
+            wk = L.width(k)
+            sk = s[:, (k_loc - r0) * nb:(k_loc - r0) * nb + wk]
+            rows = rrow[:, :(k - j - 1) * nb + wk]                             # R_j, (j+1 .. k)
+            upd = rows.T @ sk
+            tgt = loc[(j + 1) * nb:(j + 1) * nb + upd.shape[0], k_loc * nb:k_loc * nb + wk]
+            keep = np.triu(np.ones_like(upd), -(k - j - 1) * nb) > 0           # global row <= global column
+            tgt[keep] -= upd[keep]
+    np.save(os.path.join(out, "p%d.npy" % rank), loc)
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,n,nb,port", [(2, 70, 8, 29581), (3, 100, 16, 29582)])
+def test_schedule_over_gloo_matches_lapack(tmp_path, world, n, nb, port):
+    import torch.multiprocessing as mp
+    mp.spawn(_gloo_worker, args=(world, port, n, nb, str(tmp_path)), nprocs=world, join=True)
+    rng = np.random.default_rng(n)
+    m = rng.random((n, n)) - 0.5
+    a = m @ m.T + n * np.eye(n)
+    r = np.linalg.cholesky(a).T
+    L = Layout(world, nb, n)
+    for p in range(world):
+        loc = np.load(tmp_path / ("p%d.npy" % p))
+        for k_loc, j in enumerate(cdist.potrf_1d_blocks(n, nb, world, p)):
+            got = loc[:, k_loc * nb:k_loc * nb + L.width(j)]
+            want = r[:, j * nb:j * nb + L.width(j)]
+            rows = (j + 1) * nb
+            assert np.allclose(np.triu(got[:rows], -j * nb), np.triu(want[:rows], -j * nb), rtol=1e-11, atol=1e-12)
+            assert np.array_equal(np.tril(got, -j * nb - 1), np.tril(a[:, j * nb:j * nb + L.width(j)], -j * nb - 1))
