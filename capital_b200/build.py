@@ -41,7 +41,7 @@ def build(force=False, verbose=False):
 
 
 HOST_BIN = os.path.join(HERE, "host", "bin")
-HOST_MAINS = ["cacqr", "cholinv", "summa_gemm"]
+HOST_MAINS = ["cacqr", "cholinv", "summa_gemm", "potrf"]
 
 
 def build_host(force=False):

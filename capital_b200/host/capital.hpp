@@ -8,6 +8,7 @@
 //   topo::square / topo::rect            src/util/topology.h:16-143
 //   matmult::summa::invoke               src/alg/matmult/summa/summa.hpp:7-161
 //   cholesky::cholinv<>::factor          src/alg/cholesky/cholinv/cholinv.hpp:6-47
+//   cholesky::potrf1d, blas::engine::_trsm   additions without a reference counterpart (cap_potrf_1d, cap_dtrsm)
 //   qr::cacqr<>::factor                  src/alg/qr/cacqr/cacqr.hpp:219-270
 //
 // Differences that a device back end forces: all matrix storage is DEVICE memory;
@@ -149,6 +150,13 @@ public:
   static void _syrk(double* A, double* C, int64_t n, int64_t k, int64_t lda, int64_t ldc, const ArgPack_syrk<double>& p) {
     assert(p.order == Order::AblasColumnMajor);
     capital::check(cap_dsyrk(capital::handle(), chr(p.uplo), chr(p.transposeA), n, k, p.alpha, A, lda, p.beta, C, ldc), "cap_dsyrk");
+  }
+  // Not a member of the reference's engine (src/blas/interface.h:57-66 has no _trsm; its schedules multiply by explicit
+  // inverses, cholinv.hpp:113-124): op(A) X = alpha B (Left) or X op(A) = alpha B (Right), in place on B; takes the same
+  // argument pack as _trmm.  Non-unit diagonal only.
+  static void _trsm(double* A, double* B, int64_t m, int64_t n, int64_t lda, int64_t ldb, const ArgPack_trmm<double>& p) {
+    assert(p.order == Order::AblasColumnMajor);
+    capital::check(cap_dtrsm(capital::handle(), chr(p.side), chr(p.uplo), chr(p.transposeA), chr(p.diag), m, n, p.alpha, A, lda, B, ldb), "cap_dtrsm");
   }
 };
 }  // namespace blas
@@ -323,6 +331,55 @@ public:
   }
 };
 }  // namespace matmult
+
+// ------------------------------------------------------------------------------------------ cholesky::potrf1d
+// Cholesky (R only, A = R^T R) over the ranks of the runtime with the look-ahead schedule of cap_potrf_1d.  NOT a class
+// of the reference: it is the B200-native route to the Cholesky target of BASELINE.json (north_star: "on a 2x2x2 (or
+// 1D/2D) process grid") when the inverse factor that cholesky::cholinv also produces is not wanted.  The matrix lives in
+// its own distribution: block columns of width nb, block j on rank (j / P even ? j % P : P-1 - j % P), stored side by
+// side as an N x ncols_local column-major array.
+namespace cholesky {
+class potrf1d {
+public:
+  struct layout {
+    int64_t N = 0; int nb = 0, ranks = 1, rank = 0;
+    int64_t ncols_local = 0;
+    std::vector<int64_t> blocks;                            // global block-column index of every local block, in local order
+    int64_t width(int64_t j) const { const int64_t w = N - j * nb; return w < nb ? w : nb; }
+  };
+  static layout make_layout(int64_t N, int nb) {
+    auto& rt = capital::runtime::get();
+    layout L; L.N = N; L.nb = nb; L.ranks = rt.size(); L.rank = rt.rank();
+    int nblocks = 0;
+    capital::check(cap_potrf_1d_layout(N, nb, L.ranks, L.rank, &L.ncols_local, &nblocks), "cap_potrf_1d_layout");
+    const int64_t nblk = (N + nb - 1) / nb;
+    for (int64_t j = 0; j < nblk; ++j) {
+      int owner = 0, local = 0;
+      capital::check(cap_potrf_1d_block(j, L.ranks, &owner, &local), "cap_potrf_1d_block");
+      if (owner == L.rank) L.blocks.push_back(j);
+    }
+    assert((int)L.blocks.size() == nblocks);
+    return L;
+  }
+  // the reference's SPD generator (rect::_distribute_symmetric, src/matrix/structure.hpp:69-103) for this rank's columns.
+  // The generator adds N to the diagonal only where LOCAL row == LOCAL column (structure.hpp:87-89), so a shifted block
+  // gets its diagonal square generated by a second call whose local origin is the global diagonal.
+  static void distribute_symmetric(double* A_loc, int64_t lda, const layout& L) {
+    for (size_t r = 0; r < L.blocks.size(); ++r) {
+      const int64_t j = L.blocks[r], w = L.width(j), c0 = (int64_t)r * L.nb;
+      double* col = A_loc + c0 * lda;
+      capital::check(cap_fill_symmetric(capital::handle(), col, lda, L.N, w, j * L.nb, 0, 1, 1, L.N, 1), "cap_fill_symmetric");
+      if (j > 0) capital::check(cap_fill_symmetric(capital::handle(), col + j * L.nb, lda, w, w, j * L.nb, j * L.nb, 1, 1, L.N, 1), "cap_fill_symmetric");
+    }
+  }
+  // in place: the upper triangle of the global matrix becomes R; nothing below the diagonal is written
+  static void factor(double* A_loc, int64_t lda, const layout& L) {
+    auto& rt = capital::runtime::get();
+    capital::check(cap_reset_info(rt.handle()), "cap_reset_info");
+    capital::check(cap_potrf_1d(rt.handle(), rt.size() > 1 ? rt.world() : nullptr, L.N, L.nb, A_loc, lda), "cap_potrf_1d");
+  }
+};
+}  // namespace cholesky
 
 // ------------------------------------------------------------------------------------------ cholesky::cholinv
 namespace cholesky {
