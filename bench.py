@@ -233,8 +233,19 @@ def ours_arm(args):
                       "trtri_ms": ms_trtri, "trtri_tflops": fl / ms_trtri * 1e-9, "trtri_frac_of_peak": fl / ms_trtri * 1e-9 / peak,
                       "lapack_info": eng.info()}
             del S, W
+            torch.cuda.empty_cache()
+            # the matrix size of BASELINE config 3 on ONE GPU (the 8-GPU numbers of that config: profiles/r01_potrf1d_summary.txt)
+            nf = 32768
+            S = colmajor(nf, nf); eng.fill_symmetric(S, 0, 0, 1, 1, nf, True); W = colmajor(nf, nf)
+            ms_copy = time_kernel(lambda: W.copy_(S), 2)
+            ms_big = time_kernel(lambda: (W.copy_(S), eng._potrf(W, nf, "U")), 2) - ms_copy
+            fl = nf ** 3 / 3.0
+            factor.update({"potrf_n32768_ms": ms_big, "potrf_n32768_tflops": fl / ms_big * 1e-9, "potrf_n32768_frac_of_peak": fl / ms_big * 1e-9 / peak,
+                           "lapack_info_n32768": eng.info()})
+            del S, W
+            torch.cuda.empty_cache()
         except Exception as exc:  # noqa: BLE001 -- an extra, never allowed to break the headline line
-            factor = {"error": str(exc)[:200]}
+            factor = dict(factor or {}, error=str(exc)[:200])
 
     # ---- end to end through the C ABI with HOST buffers (H2D + factor + D2H inside the timed region)
     e2e = None
