@@ -15,6 +15,7 @@
  */
 #ifndef CAPITAL_B200_H_
 #define CAPITAL_B200_H_
+#include <stddef.h>
 #include <stdint.h>
 #ifdef __cplusplus
 extern "C" {
