@@ -131,9 +131,72 @@ class ClockSampler:
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons), "samples": len(sm), "power_w_max": watts}
 
 
+def measure_fp64_peak(device_index):
+    """DMMA.8x8x4 issue-rate peak measured NOW on this GPU by tools/dmma_peak (built by build()); MEASURED_PEAKS.json
+    carries no FP64 entry.  Falls back to the round-1 measurement file, and says so."""
+    exe = os.path.join(ROOT, "tools", "dmma_peak")
+    try:
+        env = dict(os.environ, CUDA_VISIBLE_DEVICES=str(device_index))
+        out = subprocess.run([exe], env=env, capture_output=True, text=True, timeout=120, check=True).stdout
+        burst, sustained, clock = 0.0, None, None
+        for row in out.splitlines():
+            if row.startswith("warps/SM"):
+                burst = max(burst, float(row.split("DMMA")[1].split()[0]))
+            elif row.startswith("sustained DMMA"):
+                sustained = float(row.split(":")[1].split()[0])
+            elif row.startswith("device="):
+                clock = row.strip()
+        if sustained:
+            return {"dmma_tflops_sustained": sustained, "dmma_tflops_burst": burst, "device": clock,
+                    "source": "tools/dmma_peak run inside this bench (register-only DMMA.8x8x4 loop, 16 warps/SM, ~3 s back to back)"}
+    except Exception as exc:  # noqa: BLE001
+        err = str(exc)[:120]
+    else:
+        err = "no sustained line"
+    if os.path.exists(FP64_PEAKS):
+        pk = json.load(open(FP64_PEAKS))
+        return {"dmma_tflops_sustained": float(pk["dmma_tflops_sustained"]), "dmma_tflops_burst": float(pk["dmma_tflops_burst"]),
+                "source": "profiles/fp64_peak.json (round-1 measurement; live tools/dmma_peak failed: %s)" % err}
+    raise SystemExit("bench.py: no FP64 peak available (tools/dmma_peak failed: %s)" % err)
+
+
+def cpu_extra_baselines(cores):
+    """cfg1 exactly through the reference's own bench main, and scaled cholinv / SUMMA runs of the
+    unmodified reference (oracle/_ref).  Seconds are the reference's own MPI_Wtime bracket, max over its ranks."""
+    ref = os.path.join(ROOT, "oracle", "_ref")
+    out = {}
+
+    def run(tag, cmd, ranks, threads, flops, parse):
+        try:
+            env = dict(os.environ, MINIMPI_NP=str(ranks), OPENBLAS_NUM_THREADS=str(threads), REF_NO_DUMP="1", MINIMPI_STAGE_MB="512")
+            txt = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=300, check=True).stdout
+            sec = parse(txt)
+            out[tag] = {"seconds": sec, "tflops": flops / sec * 1e-12, "ranks": ranks, "blas_threads": threads, "cores": ranks * threads,
+                        "cmd": " ".join(os.path.basename(c) if i == 0 else c for i, c in enumerate(cmd))}
+        except Exception as exc:  # noqa: BLE001
+            out[tag] = {"error": str(exc)[:160]}
+
+    field = lambda txt: float(dict(kv.split("=") for kv in txt.split() if "=" in kv)["seconds"])
+    last_col = lambda txt: float(txt.strip().splitlines()[-1].split()[-1])
+    m1, n1 = 65536, 256
+    for threads in sorted({1, max(1, cores // 4)}):        # bench/qr/cacqr.cpp as `cacqr 2 65536 256 1 1 1 1 0 0 0 0 5` (BASELINE config 1)
+        run("cfg1_cacqr_65536x256_4ranks_x%d" % threads, [os.path.join(ref, "b_cacqr"), "2", str(m1), str(n1), "1", "1", "1", "1", "0", "0", "0", "0", "5"],
+            4, threads, flops_cacqr2(m1, n1), last_col)
+    nc = 8192
+    run("cholinv_8192_p1", [os.path.join(ref, "ref_driver"), "cholinv", "/tmp/capital_ref_x", str(nc), "1", "0", "1", "0", "0", "0", "2", "0"],
+        1, cores, nc ** 3 / 3.0, field)
+    if cores >= 8:
+        run("cholinv_8192_2x2x2", [os.path.join(ref, "ref_driver"), "cholinv", "/tmp/capital_ref_x", str(nc), "1", "0", "1", "0", "0", "0", "2", "0"],
+            8, max(1, cores // 8), nc ** 3 / 3.0, field)
+    run("summa_8192_p1", [os.path.join(ref, "ref_driver"), "summa", "/tmp/capital_ref_x", str(nc), str(nc), str(nc), "1", "0", "0"],
+        1, cores, 2.0 * nc ** 3, field)
+    return out
+
+
 def ours_arm(args):
     import torch
     import torch.distributed as dist
+    from capital_b200 import checks
     from capital_b200 import dist as cdist
     from capital_b200.engine import Engine, colmajor
 
@@ -152,16 +215,26 @@ def ours_arm(args):
     comm = cdist.Comm(eng) if world > 1 else None
     comm_ptr = comm.ptr if comm else None
 
-    m, n = M_GLOBAL, N_COLS
-    m_loc, _ = cdist.local_rows(m, world, rank)
-    A = colmajor(m_loc, n); Q = colmajor(m_loc, n); R = colmajor(n, n)
-    eng.fill_random(A, rank)                       # bench/qr/cacqr.cpp:34: distribute_random(key = rank / c), c = 1
-
     def barrier():
         torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
+
+    # FP64 tensor peak of THIS box, measured before anything else (rank 0's GPU; the others wait at the barrier)
+    peaks = measure_fp64_peak(local_rank) if rank == 0 else None
+    barrier()
+    if world > 1:
+        box = [peaks]
+        dist.broadcast_object_list(box, src=0)
+        peaks = box[0]
+    peak = float(peaks["dmma_tflops_sustained"])
+    nominal = 40.0                                     # BASELINE.json: "~40 TFLOP/s FP64 tensor" per B200
+
+    m, n = M_GLOBAL, N_COLS
+    m_loc, _ = cdist.local_rows(m, world, rank)
+    A = colmajor(m_loc, n); Q = colmajor(m_loc, n); R = colmajor(n, n)
+    eng.fill_random(A, rank)                       # bench/qr/cacqr.cpp:34: distribute_random(key = rank / c), c = 1
 
     def step():
         eng.cacqr_factor_1d(A, Q, R, 2, comm_ptr)
@@ -186,6 +259,13 @@ def ours_arm(args):
     ms_step = ms_total / args.steps
     value = flops_cacqr2(m, n) / (ms_step * 1e-3) * 1e-12
 
+    # ---- parity of the timed result, at every N: the reference's own validators (test/qr/validate.hpp:7-52) on the device
+    orth, resid = eng.validate_cacqr_1d(A, Q, R, comm_ptr)
+    tol = 1e-13 * n
+    parity = {"orthogonality": orth, "residual": resid, "tol": tol, "lapack_info": info,
+              "metric": "||Q^T Q - I||_F / n and ||Q R - A||_F / ||A||_F of the timed factorization (cap_validate_cacqr_1d, all ranks)",
+              "ok": bool(orth <= tol and resid <= tol and info == 0)}
+
     # ---- roofline of the dominant kernels, timed live on the launching stream ------------------
     X = colmajor(n, n); G = colmajor(n, n)
     eng.cqr_gram(Q, G); eng.cholinv(G, X, n, True)
@@ -200,52 +280,24 @@ def ours_arm(args):
     ms_apply = time_kernel(lambda: eng.cqr_apply(X, A, Q))
     ms_gram = time_kernel(lambda: eng.cqr_gram(A, G))
     ms_small = time_kernel(lambda: eng.cholinv(G.clone(), X, n, True))
-    peaks = json.load(open(FP64_PEAKS)) if os.path.exists(FP64_PEAKS) else {"dmma_tflops_sustained": 36.6, "source": "fallback constant"}
-    peak = float(peaks["dmma_tflops_sustained"])
     kflops = float(m_loc) * n * n                  # algorithmic flops of one launch: triangular multiply / syrk of m_loc x n
     traffic, traffic_src = None, None
-    tpath = os.path.join(ROOT, "profiles", "r01_traffic.json")
-    if os.path.exists(tpath):
-        tj = json.load(open(tpath))
-        traffic = float(tj["dram_bytes_per_element"]) * m_loc * n     # measured DRAM bytes per panel element x elements of this launch
-        traffic_src = tj["source"]
+    for tname in ("r02_traffic.json", "r01_traffic.json"):
+        tpath = os.path.join(ROOT, "profiles", tname)
+        if os.path.exists(tpath):
+            tj = json.load(open(tpath))
+            traffic = float(tj["dram_bytes_per_element"]) * m_loc * n     # measured DRAM bytes per panel element x elements of this launch
+            traffic_src = tj["source"]
+            break
     roofline = {"bound": "tensor", "kernel": "dmma_tma_gemm_kernel<A_MC,B_KC> as Q=A*Rinv, row-panel schedule (cap_cqr_apply)", "achieved": kflops / ms_apply * 1e-9, "peak": peak,
-                "unit": "TFLOP/s", "frac": kflops / ms_apply * 1e-9 / peak, "traffic": traffic, "traffic_unit": "bytes per launch (dram read + write)",
+                "unit": "TFLOP/s", "frac": kflops / ms_apply * 1e-9 / peak, "frac_of_nominal_peak": kflops / ms_apply * 1e-9 / nominal,
+                "traffic": traffic, "traffic_unit": "bytes per launch (dram read + write)",
                 "traffic_source": traffic_src, "algorithmic_bytes_per_launch": 16.0 * m_loc * n,
-                "peak_source": "measured DMMA.8x8x4 issue-rate microkernel, sustained (tools/dmma_peak.cu -> profiles/fp64_peak.json); MEASURED_PEAKS.json has no FP64 entry",
+                "peak_source": peaks["source"], "peak_burst": peaks.get("dmma_tflops_burst"), "peak_device": peaks.get("device"),
                 "ms_per_launch": ms_apply, "algorithmic_flops_per_launch": kflops,
                 "gram": {"kernel": "dmma_tma_gemm_kernel<A_KC,B_KC> split-K + splitk_reduce (cap_cqr_gram)", "achieved": kflops / ms_gram * 1e-9, "frac": kflops / ms_gram * 1e-9 / peak, "ms_per_launch": ms_gram},
                 "potrf_trtri_ms": ms_small}
     del X, G
-
-    # ---- BASELINE config 5 beside the headline (rank 0 of a 1-GPU run only): Cholesky and triangular inverse of N = 16384
-    factor = None
-    if world == 1:
-        try:
-            nf = 16384
-            S = colmajor(nf, nf); eng.fill_symmetric(S, 0, 0, 1, 1, nf, True); W = colmajor(nf, nf)
-            ms_copy = time_kernel(lambda: W.copy_(S), 3)
-            ms_potrf = time_kernel(lambda: (W.copy_(S), eng._potrf(W, nf, "U")), 3) - ms_copy
-            ms_trtri = time_kernel(lambda: (S.copy_(W), eng._trtri(S, nf, "U", "N")), 3) - ms_copy
-            fl = nf ** 3 / 3.0
-            factor = {"workload": "potrf + trtri N=16384 FP64 (BASELINE config 5), one GPU, algorithmic flops N^3/3 each",
-                      "potrf_ms": ms_potrf, "potrf_tflops": fl / ms_potrf * 1e-9, "potrf_frac_of_peak": fl / ms_potrf * 1e-9 / peak,
-                      "trtri_ms": ms_trtri, "trtri_tflops": fl / ms_trtri * 1e-9, "trtri_frac_of_peak": fl / ms_trtri * 1e-9 / peak,
-                      "lapack_info": eng.info()}
-            del S, W
-            torch.cuda.empty_cache()
-            # the matrix size of BASELINE config 3 on ONE GPU (the 8-GPU numbers of that config: profiles/r01_potrf1d_summary.txt)
-            nf = 32768
-            S = colmajor(nf, nf); eng.fill_symmetric(S, 0, 0, 1, 1, nf, True); W = colmajor(nf, nf)
-            ms_copy = time_kernel(lambda: W.copy_(S), 2)
-            ms_big = time_kernel(lambda: (W.copy_(S), eng._potrf(W, nf, "U")), 2) - ms_copy
-            fl = nf ** 3 / 3.0
-            factor.update({"potrf_n32768_ms": ms_big, "potrf_n32768_tflops": fl / ms_big * 1e-9, "potrf_n32768_frac_of_peak": fl / ms_big * 1e-9 / peak,
-                           "lapack_info_n32768": eng.info()})
-            del S, W
-            torch.cuda.empty_cache()
-        except Exception as exc:  # noqa: BLE001 -- an extra, never allowed to break the headline line
-            factor = dict(factor or {}, error=str(exc)[:200])
 
     # ---- end to end through the C ABI with HOST buffers (H2D + factor + D2H inside the timed region)
     e2e = None
@@ -268,9 +320,57 @@ def ours_arm(args):
         sec = cdist.max_over_ranks(time.perf_counter() - t0) / e2e_steps
         e2e = {"value": flops_cacqr2(m, n) / sec * 1e-12, "unit": "TFLOP/s", "h2d_bytes_per_step": m * n * 8,
                "d2h_bytes_per_step": m * n * 8 + world * n * n * 8, "ms_per_step": sec * 1e3, "steps": e2e_steps,
+               "h2d_plus_d2h_gbs_per_gpu": 2.0 * m_loc * n * 8 / sec * 1e-9,
                "api": "cap_cacqr_factor_1d_host (pinned host A -> Q, R)"}
+        del hA, hQ, hR
     except Exception as exc:  # noqa: BLE001 -- report, never fake, a missing end-to-end number
         e2e = {"value": None, "unit": "TFLOP/s", "error": str(exc)[:200]}
+    eng.release_workspace()
+    torch.cuda.empty_cache()
+
+    # ---- the other algorithms BASELINE.json's metric and configs name, at this N, each with its own parity check ---------
+    extras = {}
+    def extra(name, fn):
+        if args.no_extras:
+            return
+        t0 = time.perf_counter()
+        try:
+            extras[name] = fn()
+        except Exception as exc:  # noqa: BLE001 -- an extra never breaks the headline line; a failed one is reported as failed
+            extras[name] = {"ok": False, "error": "%s: %s" % (type(exc).__name__, str(exc)[:300])}
+        extras[name]["wall_s"] = round(time.perf_counter() - t0, 2)
+        try:
+            eng.release_workspace()
+        except Exception:  # noqa: BLE001
+            pass
+        torch.cuda.empty_cache()
+
+    n_chol = 32768
+    extra("parity_small", lambda: {"cacqr2_1d": checks.cqr2_small_check(eng, comm_ptr, world, rank),
+                                   "potrf_1d": checks.potrf1d_small_check(eng, comm_ptr, world, rank),
+                                   "grid": checks.grid_small_check(eng, comm, world, rank, 1024),
+                                   "note": "product path vs numpy on assembled global matrices, run inside this bench process group at %d rank(s)" % world})
+    if "parity_small" in extras and "cacqr2_1d" in extras["parity_small"]:
+        ps = extras["parity_small"]
+        ps["ok"] = bool(ps["cacqr2_1d"]["ok"] and ps["potrf_1d"]["ok"] and ps["grid"]["ok"])
+    extra("cholesky", lambda: checks.cholesky_block(eng, comm_ptr, world, rank, n_chol, 2048 if world <= 2 else 1024, 3, peak))
+    extra("cholinv_grid", lambda: checks.cholinv_grid_block(eng, comm, world, rank, n_chol, 2, peak))
+    extra("summa", lambda: checks.summa_block(eng, comm, world, rank, 65536 if world == 8 else 32768, 2, peak))
+
+    # ---- BASELINE config 5 (one GPU only): Cholesky and triangular inverse of N = 16384 through the LAPACK-style entry points
+    if world == 1 and not args.no_extras:
+        def cfg5():
+            nf = 16384
+            S = colmajor(nf, nf); eng.fill_symmetric(S, 0, 0, 1, 1, nf, True); W = colmajor(nf, nf)
+            ms_copy = time_kernel(lambda: W.copy_(S), 3)
+            ms_potrf = time_kernel(lambda: (W.copy_(S), eng._potrf(W, nf, "U")), 3) - ms_copy
+            ms_trtri = time_kernel(lambda: (S.copy_(W), eng._trtri(S, nf, "U", "N")), 3) - ms_copy
+            fl = nf ** 3 / 3.0
+            return {"workload": "potrf + trtri N=16384 FP64 (BASELINE config 5), one GPU, algorithmic flops N^3/3 each",
+                    "potrf_ms": ms_potrf, "potrf_tflops": fl / ms_potrf * 1e-9, "potrf_frac_of_peak": fl / ms_potrf * 1e-9 / peak,
+                    "trtri_ms": ms_trtri, "trtri_tflops": fl / ms_trtri * 1e-9, "trtri_frac_of_peak": fl / ms_trtri * 1e-9 / peak,
+                    "lapack_info": eng.info(), "ok": eng.info() == 0}
+        extra("config5", cfg5)
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -281,9 +381,13 @@ def ours_arm(args):
             cpu = {"value": rate, "unit": "TFLOP/s", "cores": ranks_c * threads_c, "kind": "reference", "seconds": sec,
                    "sample": "CholeskyQR2 %dx%d (1/%d of the rows), unmodified reference via oracle/_ref, %d minimpi ranks x %d OpenBLAS threads" % (
                        m_sample, n, m // m_sample, ranks_c, threads_c)}
+            if not args.no_extras:
+                cpu["extra"] = cpu_extra_baselines(cores)
         except Exception as exc:  # noqa: BLE001
             cpu = {"value": None, "unit": "TFLOP/s", "error": str(exc)[:200]}
 
+    # a wrong number fails the run; an extra that could not run (exception: reported in its block) does not
+    all_ok = parity["ok"] and all(v.get("ok", True) or "error" in v for v in extras.values())
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": "TFLOP/s", "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
@@ -291,16 +395,20 @@ def ours_arm(args):
             "data": "synthetic (reference drand48 generator, bit-exact on device)",
             "config": {"workload": "CholeskyQR2 2^22x1024 FP64 (BASELINE config 2), rows dealt over %d GPU(s), NCCL allreduce of the packed Gram" % world,
                        "m": m, "n": n, "m_loc": m_loc, "grid": "1D c=1 d=%d" % world, "l2": "inputs (%.0f GiB per GPU) exceed the 126 MB L2; no flush needed" % (m_loc * n * 8 / 2 ** 30)},
-            "frac_of_fp64_peak": value / (peak * world), "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
-            "roofline": roofline, "cpu_baseline": cpu, "lapack_info": info, "config5": factor,
+            "frac_of_fp64_peak": value / (peak * world), "frac_of_measured_peak": value / (peak * world), "frac_of_nominal_peak": value / (nominal * world),
+            "fp64_peak": peaks, "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
+            "parity": parity, "parity_ok": bool(all_ok),
+            "roofline": roofline, "cpu_baseline": cpu, "vs_cpu_baseline": (value / cpu["value"]) if cpu and cpu.get("value") else None,
+            "lapack_info": info, "cholesky": extras.get("cholesky"), "cholinv_grid": extras.get("cholinv_grid"), "summa": extras.get("summa"),
+            "parity_small": extras.get("parity_small"), "config5": extras.get("config5"),
         }
         print(json.dumps(line), flush=True)
+    eng.close()                 # the handle may own a duplicate of comm: it goes first
     if comm:
         comm.close()
-    eng.close()
     if world > 1:
         dist.destroy_process_group()
-    return 0
+    return 0 if all_ok else 1
 
 
 def main():
@@ -310,6 +418,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="headline + parity + roofline + e2e only (skip the Cholesky / cholinv / SUMMA blocks)")
     args = ap.parse_args()
     return reference_arm(args) if args.impl == "reference" else ours_arm(args)
 

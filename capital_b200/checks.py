@@ -1,0 +1,336 @@
+"""Multi-rank parity checks and timed blocks shared by bench.py, tools/ and the -m gpu tests.
+
+Everything here runs the PRODUCT path (the C ABI through capital_b200.engine) and compares it with an
+independent checker: numpy on assembled global matrices at small sizes, and size-independent sampled
+identities (probe vectors, sampled tiles; torch fp64 products as the checker) at BASELINE sizes.
+None of it imports oracle/ -- bench.py may only touch the oracle in its cpu_baseline leg.
+
+Metrics follow the reference's validators: test/qr/validate.hpp:7-52 (orthogonality ||Q^T Q - I||_F / n,
+residual ||Q R - A||_F / ||A||_F) and test/cholesky/validate.hpp:7-48 (||R^T R - A||_F / ||A||_F).
+"""
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from . import dist as cdist
+from .engine import colmajor, to_colmajor
+
+TOL_FACTOR = 1e-11          # relative factor difference against a reference factor (BASELINE.json north_star)
+
+
+def _world():
+    return dist.get_world_size() if dist.is_initialized() else 1
+
+
+def barrier():
+    torch.cuda.synchronize()
+    if _world() > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+
+
+def timed(fn, iters):
+    """Mean milliseconds of `fn` over `iters` calls: CUDA events on the current stream, barrier + synchronize on
+    both sides, max over ranks (the reference's PMPI_Allreduce(MAX), bench/qr/cacqr.cpp:52)."""
+    barrier()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(iters):
+        fn()
+    b.record()
+    barrier()
+    return cdist.max_over_ranks(a.elapsed_time(b)) / iters
+
+
+def _allreduce(t):
+    if _world() > 1:
+        dist.all_reduce(t)
+    return t
+
+
+def _all_ok(flag):
+    t = torch.tensor([0.0 if flag else 1.0], dtype=torch.float64, device="cuda")
+    return float(_allreduce(t).item()) == 0.0
+
+
+def _max(value):
+    t = torch.tensor([float(value)], dtype=torch.float64, device="cuda")
+    if _world() > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def _gather_list(flat):
+    world = _world()
+    if world == 1:
+        return [flat]
+    parts = [torch.empty_like(flat) for _ in range(world)]
+    dist.all_gather(parts, flat)
+    return parts
+
+
+# --------------------------------------------------------------------------------------------- CholeskyQR2, 1D
+def cqr2_small_check(eng, comm_ptr, world, rank, m=10001, n=192):
+    """Sharded CholeskyQR2 (rows dealt cyclically, ragged m) against numpy's QR of the assembled matrix."""
+    m_loc, owned = cdist.local_rows(m, world, rank)
+    A = colmajor(m_loc, n, fill=0.0)
+    eng.fill_random(A[:owned], rank)
+    Q = colmajor(m_loc, n); R = colmajor(n, n)
+    eng.reset_info(); eng.cacqr_factor_1d(A, Q, R, 2, comm_ptr); torch.cuda.synchronize()
+    a_parts = _gather_list(A.t().contiguous()); q_parts = _gather_list(Q.t().contiguous()); r_parts = _gather_list(R.t().contiguous())
+    Ag = np.zeros((m_loc * world, n)); Qg = np.zeros((m_loc * world, n))
+    for r in range(world):
+        Ag[r::world] = a_parts[r].t().cpu().numpy(); Qg[r::world] = q_parts[r].t().cpu().numpy()
+    Ag, Qg = Ag[:m], Qg[:m]
+    Qr, Rr = np.linalg.qr(Ag)
+    sg = np.sign(np.diag(Rr)); Qr = Qr * sg; Rr = (Rr.T * sg).T
+    rel = lambda x, y: float(np.linalg.norm(x - y) / np.linalg.norm(y))
+    same = all(torch.equal(r_parts[0], x) for x in r_parts)
+    out = {"m": m, "n": n, "dQ": rel(Qg, Qr), "dR": rel(R.cpu().numpy(), Rr), "replicated_R_bitwise": bool(same), "info": eng.info()}
+    out["ok"] = _all_ok(out["dQ"] <= TOL_FACTOR and out["dR"] <= TOL_FACTOR and same and out["info"] == 0)
+    return out
+
+
+# --------------------------------------------------------------------------------------------- cap_potrf_1d
+def potrf1d_local_matrix(eng, N, nb, world, rank):
+    """This rank's block columns of the reference's SPD matrix (distribute_symmetric, src/matrix/structure.hpp:69-103,
+    one process: every entry a function of its global (row, column)), side by side in cap_potrf_1d's layout."""
+    mine = cdist.potrf_1d_blocks(N, nb, world, rank)
+    widths = [min(nb, N - j * nb) for j in mine]
+    A0 = colmajor(N, max(sum(widths), 1))
+    for r, (j, w) in enumerate(zip(mine, widths)):
+        eng.fill_symmetric(A0[:, r * nb:r * nb + w], j * nb, 0, 1, 1, N, True)
+        if j > 0:   # the generator adds N where LOCAL row == LOCAL column (structure.hpp:87-89): redo it for the shifted block
+            A0[:, r * nb:r * nb + w].diagonal(-j * nb).add_(float(N))
+    return A0, mine, widths
+
+
+def potrf1d_sampled_residual(A0, A, mine, widths, nb, N, probes=8):
+    """||(R^T R - A) X||_F / ||A X||_F for a random N x probes X, with R and A held as block columns.
+    (R X) needs one all-reduce; (A X)[J] = A[:, J]^T X because A is symmetric; the checker's products are torch's."""
+    gen = torch.Generator(device="cpu"); gen.manual_seed(1234)
+    X = torch.randn((N, probes), dtype=torch.float64, generator=gen).cuda()
+    ncols = sum(widths)
+    Rl = A[:, :max(ncols, 1)].clone()
+    rows = []
+    for r, (j, w) in enumerate(zip(mine, widths)):
+        Rl[:, r * nb:r * nb + w].triu_(-j * nb)
+        rows.append(X[j * nb:j * nb + w])
+    xl = torch.cat(rows) if rows else torch.zeros((1, probes), dtype=torch.float64, device="cuda")
+    if not rows:
+        Rl.zero_()
+    w_ = _allreduce(Rl @ xl)                        # R X
+    z = Rl.t() @ w_                                  # (R^T R X)[J]
+    y = A0[:, :max(ncols, 1)].t() @ X if rows else torch.zeros_like(z)
+    acc = torch.stack([((z - y) ** 2).sum(), (y ** 2).sum()])
+    _allreduce(acc)
+    return float(torch.sqrt(acc[0] / acc[1]).item())
+
+
+def potrf1d_small_check(eng, comm_ptr, world, rank, N=2048 + 128, nb=128):
+    """Every rank's block columns of the look-ahead Cholesky against numpy's factor of the same matrix (ragged last block)."""
+    A0, mine, widths = potrf1d_local_matrix(eng, N, nb, world, rank)
+    A = colmajor(N, A0.shape[1]); A.copy_(A0)
+    eng.reset_info(); eng.potrf_1d(A, N, nb, comm_ptr); torch.cuda.synchronize()
+    F = colmajor(N, N); eng.fill_symmetric(F, 0, 0, 1, 1, N, True)
+    Rref = torch.from_numpy(np.ascontiguousarray(np.linalg.cholesky(F.cpu().numpy()).T)).cuda()
+    worst, low_ok = 0.0, True
+    for r, (j, w) in enumerate(zip(mine, widths)):
+        got, want = torch.triu(A[:, r * nb:r * nb + w], -j * nb), torch.triu(Rref[:, j * nb:j * nb + w], -j * nb)
+        worst = max(worst, float((got - want).norm() / want.norm()))
+        low_ok = low_ok and bool(torch.equal(torch.tril(A[:, r * nb:r * nb + w], -j * nb - 1), torch.tril(A0[:, r * nb:r * nb + w], -j * nb - 1)))
+    out = {"N": N, "nb": nb, "rel_vs_numpy": _max(worst), "lower_untouched": _all_ok(low_ok), "info": eng.info()}
+    out["ok"] = _all_ok(worst <= TOL_FACTOR and low_ok and out["info"] == 0)
+    return out
+
+
+def cholesky_block(eng, comm_ptr, world, rank, N, nb, iters=3, peak=36.6):
+    """cap_potrf_1d of the N x N reference SPD matrix over `world` ranks: ms (restoring copy timed alone and
+    subtracted), TFLOP/s on N^3/3, sampled residual."""
+    A0, mine, widths = potrf1d_local_matrix(eng, N, nb, world, rank)
+    A = colmajor(N, A0.shape[1])
+    for _ in range(2):
+        A.copy_(A0); eng.potrf_1d(A, N, nb, comm_ptr)
+    t_copy = timed(lambda: A.copy_(A0), iters)
+    eng.reset_info()
+    ms = timed(lambda: (A.copy_(A0), eng.potrf_1d(A, N, nb, comm_ptr)), iters) - t_copy
+    info = eng.info()
+    resid = potrf1d_sampled_residual(A0, A, mine, widths, nb, N)
+    tf = N ** 3 / 3.0 / ms * 1e-9
+    tol = 1e-13 * N
+    return {"workload": "cap_potrf_1d N=%d nb=%d, block columns dealt 1-D over %d GPU(s), algorithmic flops N^3/3" % (N, nb, world),
+            "N": N, "nb": nb, "ms": ms, "tflops": tf, "frac_of_measured_peak": tf / (peak * world), "frac_of_nominal_peak": tf / (40.0 * world),
+            "resid_sampled": resid, "resid_metric": "||(R^T R - A) X||_F / ||A X||_F, X = N x 8 gaussian probes", "tol": tol,
+            "lapack_info": info, "ok": bool(resid <= tol and info == 0)}
+
+
+# --------------------------------------------------------------------------------------------- process grid
+def grid_small_check(eng, comm, world, rank, N=1024, verbose=False):
+    """SUMMA gemm / trmm / syrk, distributed cholinv and 3D CholeskyQR on the default grid of `world` ranks against numpy
+    on the assembled global matrices.  Returns {name: relative error}, ok."""
+    c = cdist.default_depth(world)
+    grid = cdist.Grid(eng, comm, c)
+    d, x, y = grid.d, grid.x, grid.y
+    rng = np.random.default_rng(7)
+    A = rng.random((N, N)); B = rng.random((N, N)); C0 = rng.random((N, N))
+    T = np.triu(rng.random((N, N))) + N * np.eye(N)
+    S = rng.random((N, N)); S = S + S.T + 2 * N * np.eye(N)
+    loc = lambda g: to_colmajor(np.ascontiguousarray(cdist.cyclic_block(g, x, y, d)))
+    l = N // d
+    errs, ok = {}, True
+
+    def gather(t):
+        parts = _gather_list(t.t().contiguous())
+        blocks = {}
+        for r in range(world):
+            xx, yy, zz = cdist.grid_coords(r, c, d)
+            if zz == 0:
+                blocks[(xx, yy)] = parts[r].t().cpu().numpy()
+        return cdist.assemble_cyclic(blocks, d)
+
+    def report(name, got, ref, tol=TOL_FACTOR):
+        nonlocal ok
+        err = float(np.linalg.norm(got - ref) / np.linalg.norm(ref))
+        errs[name] = err
+        ok = ok and err <= tol
+        if verbose and rank == 0:
+            print("%-34s rel err %.2e %s" % (name, err, "ok" if err <= tol else "FAIL"), flush=True)
+
+    a, b, cm = loc(A), loc(B), loc(C0)
+    eng.summa_gemm(grid, a, b, cm, l, l, l, "N", "N", 1.5, 0.5); torch.cuda.synchronize()
+    report("summa gemm NN alpha beta", gather(cm), 1.5 * A @ B + 0.5 * C0)
+    t, b = loc(T), loc(B)
+    eng.summa_trmm(grid, t, b, l, l, "L", "U", "N", "N", 1.0); torch.cuda.synchronize()
+    report("summa trmm L U N", gather(b), T @ B)
+    b = loc(B)
+    eng.summa_trmm(grid, t, b, l, l, "R", "U", "N", "N", -1.0); torch.cuda.synchronize()
+    report("summa trmm R U N", gather(b), -B @ T)
+    tt = colmajor(l, l); eng.grid_transpose(grid, t, tt)      # cholinv.hpp:116-118: Left/Upper/Trans takes the grid-transposed block
+    b = loc(B)
+    eng.summa_trmm(grid, tt, b, l, l, "L", "U", "T", "N", 1.0); torch.cuda.synchronize()
+    report("summa trmm L U T (transposed T)", gather(b), T.T @ B)
+    a, cm = loc(A), loc(S)
+    eng.summa_syrk(grid, a, cm, l, l, "U", "T", -1.0, 1.0); torch.cuda.synchronize()
+    report("summa syrk U T", np.triu(gather(cm)), np.triu(S - A.T @ A))
+    for ci in (True, False):
+        s_loc, xinv = loc(S), colmajor(l, l)
+        eng.reset_info()
+        eng.cholinv_factor(grid, s_loc, xinv, ci, 1, max(256, N // 4)); torch.cuda.synchronize()
+        R = np.linalg.cholesky(S).T
+        report("cholinv R  (complete_inv=%d)" % ci, gather(s_loc), R)
+        Xg, Xr = gather(xinv), np.linalg.inv(R)
+        if not ci:   # the top-level off-diagonal block of the inverse is left unset (cholinv.hpp:147)
+            Xg = Xg.copy(); Xr = Xr.copy()
+            top = np.arange(N).reshape(-1, d)[: l >> 1].ravel(); bot = np.arange(N).reshape(-1, d)[l >> 1:].ravel()
+            Xg[np.ix_(top, bot)] = 0; Xr[np.ix_(top, bot)] = 0
+        report("cholinv Rinv (complete_inv=%d)" % ci, Xg, Xr)
+        ok = ok and eng.info() == 0
+        if ci:
+            # device validator (cholesky::validate::residual) against the same metric in numpy, on a clean and on a
+            # deliberately damaged factor (so that agreement is not just "both tiny")
+            for damage in (False, True):
+                if damage and rank == 0:
+                    s_loc[0, 0] *= 1.5
+                got = eng.validate_cholinv(grid, loc(S), s_loc)
+                Rg = gather(s_loc)
+                ref = float(np.linalg.norm(np.triu(Rg.T @ Rg - S)) / np.linalg.norm(np.triu(S)))
+                good = (abs(got - ref) <= 1e-8 * ref) if damage else (got <= 1e-14 and ref <= 1e-14)
+                errs["validate cholinv%s (device, numpy)" % (" damaged" if damage else "")] = [got, ref]
+                ok = ok and good
+                if verbose and rank == 0:
+                    print("%-34s device %.3e numpy %.3e %s" % ("validate cholinv%s" % (" (damaged)" if damage else ""), got, ref, "ok" if good else "FAIL"), flush=True)
+    M = 8 * N
+    Atall = rng.random((M, N))
+    a_loc = loc(Atall); ml = M // d
+    for iters in (1, 2):
+        q_loc, r_loc = colmajor(ml, l), colmajor(l, l)
+        eng.reset_info()
+        eng.cacqr_factor_3d(grid, a_loc, q_loc, r_loc, iters, None, 1, max(256, N // 4)); torch.cuda.synchronize()
+        Qr, Rr = np.linalg.qr(Atall)
+        sg = np.sign(np.diag(Rr)); Qr = Qr * sg; Rr = (Rr.T * sg).T
+        Qg, Rg = gather(q_loc), gather(r_loc)
+        report("3D CQR%d R" % iters, Rg, Rr, TOL_FACTOR if iters == 2 else 1e-9)
+        report("3D CQR%d Q" % iters, Qg, Qr, TOL_FACTOR if iters == 2 else 1e-9)
+        orth = float(np.linalg.norm(Qg.T @ Qg - np.eye(N)))
+        errs["3D CQR%d ||Q^T Q - I||_F" % iters] = orth
+        good = orth <= (1e-13 * N if iters == 2 else 1e-9)
+        ok = ok and good and eng.info() == 0
+        if verbose and rank == 0:
+            print("%-34s %.2e %s" % ("3D CQR%d ||Q^T Q - I||_F" % iters, orth, "ok" if good else "FAIL"), flush=True)
+        if iters == 2:
+            for damage in (False, True):
+                if damage and rank == 0:
+                    q_loc[0, 0] += 0.25
+                o_dev, r_dev = eng.validate_cacqr_3d(grid, a_loc, q_loc, r_loc)
+                Qg = gather(q_loc)
+                o_ref = float(np.linalg.norm(Qg.T @ Qg - np.eye(N)) / N)
+                r_ref = float(np.linalg.norm(Qg @ Rg - Atall) / np.linalg.norm(Atall))
+                good = (abs(o_dev - o_ref) <= 1e-8 * o_ref and abs(r_dev - r_ref) <= 1e-8 * r_ref) if damage else (o_dev <= 1e-14 and r_dev <= 1e-14)
+                errs["validate 3D CQR2%s (orth dev, np, resid dev, np)" % (" damaged" if damage else "")] = [o_dev, o_ref, r_dev, r_ref]
+                ok = ok and good
+                if verbose and rank == 0:
+                    print("%-34s orth %.3e / %.3e  resid %.3e / %.3e %s" % ("validate 3D CQR2%s" % (" (damaged)" if damage else ""), o_dev, o_ref, r_dev, r_ref, "ok" if good else "FAIL"), flush=True)
+    grid.close()
+    return {"N": N, "grid": "%dx%dx%d" % (c, d, d), "worst_rel_err": max(v for v in errs.values() if not isinstance(v, list)) if errs else None,
+            "errors": errs, "ok": _all_ok(ok)}
+
+
+def cholinv_grid_block(eng, comm, world, rank, N, iters=2, peak=36.6, bc_global=2048):
+    """cholesky::cholinv::factor (the reference's schedule, bench/cholesky/cholinv.cpp:15-59) of the N x N reference SPD
+    matrix on the default c x d x d grid of `world` ranks, complete_inv = 0 and 1; residual by the device validator."""
+    c = cdist.default_depth(world)
+    grid = cdist.Grid(eng, comm, c)
+    d = grid.d
+    l = N // d
+    S = colmajor(l, l); eng.fill_symmetric(S, grid.x, grid.y, d, d, N, True)
+    W, X = colmajor(l, l), colmajor(l, l)
+    t_copy = timed(lambda: W.copy_(S), iters)
+    out = {"workload": "cholinv::factor N=%d on the %dx%dx%d grid (reference schedule, base case %d), TFLOP/s on N^3/3" % (N, c, d, d, bc_global),
+           "N": N, "grid": "%dx%dx%d" % (c, d, d), "tol": 1e-13 * N}
+    ok = True
+    for ci in (0, 1):
+        W.copy_(S); eng.cholinv_factor(grid, W, X, bool(ci), 1, bc_global)
+        eng.reset_info()
+        ms = timed(lambda: (W.copy_(S), eng.cholinv_factor(grid, W, X, bool(ci), 1, bc_global)), iters) - t_copy
+        info = eng.info()
+        resid = eng.validate_cholinv(grid, S, W)
+        tf = N ** 3 / 3.0 / ms * 1e-9
+        out["ci%d" % ci] = {"ms": ms, "tflops": tf, "frac_of_measured_peak": tf / (peak * world), "resid": resid, "lapack_info": info}
+        ok = ok and resid <= 1e-13 * N and info == 0
+    out["resid_metric"] = "||R^T R - A||_F / ||A||_F over the upper triangle (cap_validate_cholinv, test/cholesky/validate.hpp:7-30)"
+    out["ok"] = _all_ok(ok)
+    grid.close()
+    return out
+
+
+def summa_block(eng, comm, world, rank, N, iters=2, peak=36.6, sample=64):
+    """matmult::summa::invoke gemm (bench/matmult/summa_gemm.cpp:19-38) C = A B of global N x N random matrices on the
+    default grid; a sampled sample x sample tile of every rank's C block is recomputed from the operand slices of the
+    ranks in its grid row / column (torch fp64 products as the checker)."""
+    c = cdist.default_depth(world)
+    grid = cdist.Grid(eng, comm, c)
+    d, x, y = grid.d, grid.x, grid.y
+    l = N // d
+    A, B, C = colmajor(l, l), colmajor(l, l), colmajor(l, l)
+    eng.fill_random(A, x + d * y); eng.fill_random(B, 1000 + x + d * y)     # layers hold replicas: the key ignores z
+    eng.summa_gemm(grid, A, B, C, l, l, l, "N", "N", 1.0, 0.0)
+    ms = timed(lambda: eng.summa_gemm(grid, A, B, C, l, l, l, "N", "N", 1.0, 0.0), iters)
+    # sampled tile: rows I, columns J of the local C block = sum_t A_loc(t, y)[I, :] B_loc(x, t)[:, J]
+    gen = torch.Generator(device="cpu"); gen.manual_seed(99)
+    I = torch.randperm(l, generator=gen)[:sample].cuda(); J = torch.randperm(l, generator=gen)[:sample].cuda()
+    a_parts = _gather_list(A[I, :].contiguous()); b_parts = _gather_list(B[:, J].contiguous())
+    ref = torch.zeros((I.numel(), J.numel()), dtype=torch.float64, device="cuda")
+    for t in range(d):
+        ra = 0 + c * (t + d * y)          # rank of (x = t, y, z = 0): z fastest, then x, then y (topology.h:80-95)
+        rb = 0 + c * (x + d * t)          # rank of (x, y = t, z = 0)
+        ref += a_parts[ra] @ b_parts[rb]
+    got = C[I, :][:, J]
+    err = float(((got - ref).norm() / ref.norm()).item())
+    tf = 2.0 * N ** 3 / ms * 1e-9
+    out = {"workload": "summa gemm N=%d on the %dx%dx%d grid, flops 2 N^3" % (N, c, d, d), "N": N, "grid": "%dx%dx%d" % (c, d, d), "ms": ms,
+           "tflops": tf, "frac_of_measured_peak": tf / (peak * world), "tile_rel_err": _max(err),
+           "check": "%dx%d sampled tile of every rank's C block against torch fp64 products of the gathered operand slices" % (sample, sample),
+           "tol": 1e-12}
+    out["ok"] = _all_ok(err <= 1e-12)
+    grid.close()
+    return out

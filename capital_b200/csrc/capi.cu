@@ -134,6 +134,13 @@ int cap_workspace(cap_handle_t h, int slot, size_t bytes, double** out) {
   return CAP_OK;
 }
 
+int cap_release_workspace(cap_handle_t h) {
+  CUDA_TRY(cudaSetDevice(h->device));
+  CUDA_TRY(cudaDeviceSynchronize());
+  for (auto& w : h->ws) if (w.ptr) { CUDA_TRY(cudaFree(w.ptr)); w.ptr = nullptr; w.bytes = 0; }
+  return CAP_OK;
+}
+
 // ------------------------------------------------------------------------------------------ memory
 int cap_malloc(void** p, size_t bytes) {
   if (cudaMalloc(p, bytes) != cudaSuccess) { cudaGetLastError(); return cap_fail(CAP_ERR_ALLOC, "cap_malloc", "cudaMalloc failed"); }

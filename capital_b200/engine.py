@@ -59,6 +59,10 @@ class Engine:
     def set_host_chunk_bytes(self, nbytes):
         _lib.check(self.lib.cap_set_host_chunk_bytes(self.h, int(nbytes)), "cap_set_host_chunk_bytes")
 
+    def release_workspace(self):
+        """Synchronise and free the library-owned scratch (grown on demand, otherwise kept until close())."""
+        _lib.check(self.lib.cap_release_workspace(self.h), "cap_release_workspace")
+
     def close(self):
         if self.h:
             self.lib.cap_destroy(self.h)

@@ -42,6 +42,9 @@ long long cap_kernel_launches(cap_handle_t h);               /* number of kernel
 int cap_set_engine(cap_handle_t h, int engine);
 /* row-chunk size (bytes, default 1 GiB) of the pipelined host entry point cap_cacqr_factor_1d_host */
 int cap_set_host_chunk_bytes(cap_handle_t h, size_t bytes);
+/* synchronise the device and free every library-owned workspace slot (they are grown on demand and otherwise kept
+ * until cap_destroy); a caller that moves from one large problem to another uses this to return the HBM */
+int cap_release_workspace(cap_handle_t h);
 
 /* ---- memory (matrix<>::_assemble / _destroy_, src/matrix/structure.hpp:4-24, matrix.hpp:158) -- */
 int cap_malloc(void** dptr, size_t bytes);
