@@ -103,6 +103,13 @@ int cap_destroy(cap_handle_t h) {
     cudaStreamDestroy(h->gather_stream);
     for (cudaEvent_t e : {h->ev_panel[0], h->ev_panel[1], h->ev_u1, h->ev_trmm, h->ev_gath[0], h->ev_gath[1], h->ev_u2}) cudaEventDestroy(e);
   }
+  if (h->xchg_stream) {
+    cudaStreamDestroy(h->xchg_stream); cudaStreamDestroy(h->sig_stream);
+    for (int i = 0; i < cap_handle_s::RING; ++i)
+      for (cudaEvent_t e : {h->ev_leaf[i], h->ev_csolve[i], h->ev_solve[i], h->ev_xchg[i], h->ev_xpush[i], h->ev_r1[i], h->ev_r2a[i], h->ev_r2[i]}) cudaEventDestroy(e);
+    cudaFree(h->sig_scratch);
+  }
+  if (h->peer1d) { cudaDeviceSynchronize(); cap_peer_free(h->peer1d); h->peer1d = nullptr; }
   if (h->dup_comm) cap_comm_destroy(h->dup_comm);
   cudaStreamDestroy(h->own_stream);
   cudaStreamDestroy(h->copy_stream);
@@ -126,7 +133,7 @@ int cap_reset_info(cap_handle_t h) { CUDA_TRY(cudaMemsetAsync(h->info_dev, 0, si
 int cap_workspace(cap_handle_t h, int slot, size_t bytes, double** out) {
   auto& w = h->ws[slot];
   if (w.bytes < bytes) {
-    if (w.ptr) { CUDA_TRY(cudaStreamSynchronize(h->stream)); CUDA_TRY(cudaFree(w.ptr)); w.ptr = nullptr; w.bytes = 0; }
+    if (w.ptr) { CUDA_TRY(cudaDeviceSynchronize()); CUDA_TRY(cudaFree(w.ptr)); w.ptr = nullptr; w.bytes = 0; }   // every stream of the handle may be using the slot
     if (cudaMalloc(&w.ptr, bytes) != cudaSuccess) { cudaGetLastError(); return cap_fail(CAP_ERR_ALLOC, "workspace", "cudaMalloc failed"); }
     w.bytes = bytes;
   }
@@ -263,7 +270,7 @@ static int gemm_launch(cap_handle_t h, GemmParams p, bool ta, bool tb, int want_
     } else if (tri_sq) { tp.sched = SCHED_TRI; tp.units = ntiles * ksplit; }
     else { tp.sched = (p.khi_mode == KR_TILE_M) ? SCHED_TM_DESC : SCHED_RASTER; tp.units = ntiles * ksplit; }
     tp.c_vec2 = (aligned16(tp.C, tp.ldc) && (beta == 0.0 || ksplit > 1 || aligned16(tp.Cin, tp.ldcin))) ? 1 : 0;
-    const int grid = std::min(tp.units, h->num_sms);
+    const int grid = (int)std::min<int64_t>(tp.units, (int64_t)h->num_sms * std::max(1, h->grid_mult));
     const bool akc = ta, bkc = !tb;
     if (akc) { if (bkc) launch_tma_t<true, true>(h, ma, mb, tp, grid); else launch_tma_t<true, false>(h, ma, mb, tp, grid); }
     else     { if (bkc) launch_tma_t<false, true>(h, ma, mb, tp, grid); else launch_tma_t<false, false>(h, ma, mb, tp, grid); }
@@ -295,6 +302,17 @@ static int gemm_launch(cap_handle_t h, GemmParams p, bool ta, bool tb, int want_
 int cap_set_host_chunk_bytes(cap_handle_t h, size_t bytes) {
   if (bytes < 4096) return cap_fail(CAP_ERR_ARG, "cap_set_host_chunk_bytes", "chunk too small");
   h->host_chunk_bytes = bytes;
+  return CAP_OK;
+}
+
+int cap_set_peer_exchange(cap_handle_t h, int mode) {
+  if (mode < -1 || mode > 1) return cap_fail(CAP_ERR_ARG, "cap_set_peer_exchange", "-1 = peer copy engines when CUDA IPC works, 0 = NCCL only, 1 = peer copy engines required");
+  h->peer_exchange = mode;
+  return CAP_OK;
+}
+int cap_set_update_grid(cap_handle_t h, int ctas_per_sm) {
+  if (ctas_per_sm < 0 || ctas_per_sm > 64) return cap_fail(CAP_ERR_ARG, "cap_set_update_grid", "0 = persistent grid (one CTA per SM, SM-capped beside a chain), k > 0 = k x #SMs CTAs");
+  h->lookahead_grid_mult = ctas_per_sm;
   return CAP_OK;
 }
 

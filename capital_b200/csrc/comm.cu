@@ -6,6 +6,7 @@
 
 #include <nccl.h>
 #include <cstring>
+#include <vector>
 
 struct cap_comm_s {
   ncclComm_t comm;
@@ -84,5 +85,83 @@ int cap_sendrecv(cap_handle_t h, cap_comm_t c, const double* send, double* recv,
   NCCL_TRY(ncclSend(send, (size_t)count, ncclDouble, peer, c->comm, h->stream));
   NCCL_TRY(ncclRecv(recv, (size_t)count, ncclDouble, peer, c->comm, h->stream));
   NCCL_TRY(ncclGroupEnd());
+  return CAP_OK;
+}
+
+// ------------------------------------------------------------------------------------------ peer-mapped buffers
+// cap_peer_alloc: collective over `comm`.  Every rank cudaMallocs `bytes` (zeroed), the 64-byte CUDA IPC handles are
+// all-gathered through NCCL (the only NCCL call of this path), and every other rank's buffer is opened with
+// cudaIpcOpenMemHandle, which also enables peer access over NVLink.  If ANY rank cannot map a peer, every rank gets
+// CAP_ERR_UNSUPPORTED (agreed by a second tiny collective) and the caller keeps its NCCL path.
+int cap_peer_alloc(cap_handle_s* h, cap_comm_s* comm, size_t bytes, cap_peer_s** out) {
+  *out = nullptr;
+  if (!comm || comm->size < 2 || comm->size > CAP_PEER_MAX) return cap_fail(CAP_ERR_UNSUPPORTED, "cap_peer_alloc", "needs 2..16 ranks");
+  const int P = comm->size, me = comm->rank;
+  cap_peer_s* p = new cap_peer_s();
+  p->rank = me; p->size = P; p->bytes = bytes; p->comm = comm;
+  int bad = 0;
+  void* local = nullptr;
+  if (cudaMalloc(&local, bytes) != cudaSuccess) { cudaGetLastError(); bad = 1; }
+  cudaIpcMemHandle_t mine;
+  memset(&mine, 0, sizeof(mine));
+  if (!bad && (cudaMemset(local, 0, bytes) != cudaSuccess || cudaIpcGetMemHandle(&mine, local) != cudaSuccess)) { cudaGetLastError(); bad = 1; }
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "CUDA IPC handles are 64 bytes");
+  char* stage = nullptr;                                   // [P handles][P status words]
+  const size_t hb = sizeof(cudaIpcMemHandle_t);
+  if (cudaMalloc((void**)&stage, (size_t)P * hb + (size_t)P * hb) != cudaSuccess) { cudaGetLastError(); delete p; if (local) cudaFree(local); return cap_fail(CAP_ERR_ALLOC, "cap_peer_alloc", "staging"); }
+  std::vector<cudaIpcMemHandle_t> all(P);
+  cudaMemcpy(stage + (size_t)me * hb, &mine, hb, cudaMemcpyHostToDevice);
+  cudaStreamSynchronize(h->stream);
+  ncclResult_t nr = ncclAllGather(stage + (size_t)me * hb, stage, hb, ncclChar, comm->comm, h->stream);
+  if (nr != ncclSuccess || cudaStreamSynchronize(h->stream) != cudaSuccess) { cudaFree(stage); if (local) cudaFree(local); delete p; return cap_fail(CAP_ERR_NCCL, "cap_peer_alloc", "handle exchange failed"); }
+  cudaMemcpy(all.data(), stage, (size_t)P * hb, cudaMemcpyDeviceToHost);
+  p->ptr[me] = (char*)local;
+  for (int r = 0; r < P && !bad; ++r) {
+    if (r == me) continue;
+    void* q = nullptr;
+    if (cudaIpcOpenMemHandle(&q, all[r], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); bad = 1; break; }
+    p->ptr[r] = (char*)q;
+  }
+  // agree on the outcome: sum of the per-rank failure flags
+  float flag = (float)bad, total = 0.f;
+  float* dflag = (float*)(stage + (size_t)P * hb);
+  cudaMemcpy(dflag, &flag, sizeof(float), cudaMemcpyHostToDevice);
+  nr = ncclAllReduce(dflag, dflag, 1, ncclFloat, ncclSum, comm->comm, h->stream);
+  cudaStreamSynchronize(h->stream);
+  cudaMemcpy(&total, dflag, sizeof(float), cudaMemcpyDeviceToHost);
+  cudaFree(stage);
+  if (nr != ncclSuccess || total != 0.f) {
+    cap_peer_free(p);
+    return cap_fail(CAP_ERR_UNSUPPORTED, "cap_peer_alloc", "CUDA IPC peer mapping is not available between these ranks");
+  }
+  *out = p;
+  return CAP_OK;
+}
+
+// Collective variant (re-allocation in mid-job): every rank closes its mappings, all meet, then the exporters free.
+int cap_peer_free_collective(cap_handle_s* h, cap_peer_s* p) {
+  if (!p) return CAP_OK;
+  cudaDeviceSynchronize();
+  for (int r = 0; r < p->size; ++r)
+    if (r != p->rank && p->ptr[r]) { cudaIpcCloseMemHandle(p->ptr[r]); p->ptr[r] = nullptr; }
+  float* d = nullptr;
+  if (p->comm && cudaMalloc((void**)&d, sizeof(float)) == cudaSuccess) {
+    cudaMemset(d, 0, sizeof(float));
+    ncclAllReduce(d, d, 1, ncclFloat, ncclSum, p->comm->comm, h->stream);
+    cudaStreamSynchronize(h->stream);
+    cudaFree(d);
+  }
+  return cap_peer_free(p);
+}
+
+// Not collective: the caller makes sure (device synchronised, a barrier or the end of the job) that no peer still writes here.
+int cap_peer_free(cap_peer_s* p) {
+  if (!p) return CAP_OK;
+  for (int r = 0; r < p->size; ++r) {
+    if (!p->ptr[r]) continue;
+    if (r == p->rank) cudaFree(p->ptr[r]); else cudaIpcCloseMemHandle(p->ptr[r]);
+  }
+  cudaGetLastError();
+  delete p;
   return CAP_OK;
 }

@@ -15,6 +15,21 @@ enum { CAP_WS_GEMM_SPLITK = 0, CAP_WS_TRI = 1, CAP_WS_PANEL = 2, CAP_WS_FACTOR =
 
 struct cap_ws_slot { void* ptr = nullptr; size_t bytes = 0; };
 
+// Symmetric peer-mapped buffer (comm.cu): every rank of a communicator owns `bytes` of device memory and has every other
+// rank's buffer mapped through CUDA IPC, so copy engines (cudaMemcpyAsync) and kernels can write into a peer's HBM over
+// NVLink / NVSwitch without any NCCL kernel resident on an SM.
+enum { CAP_PEER_MAX = 16 };
+struct cap_peer_s {
+  int rank = 0, size = 1;
+  size_t bytes = 0;
+  char* ptr[CAP_PEER_MAX] = {};        // ptr[rank] = the local allocation
+  struct cap_comm_s* comm = nullptr;   // the communicator it was made for (not owned)
+  uint32_t seq = 0;                    // monotonic signal counter (same value on every rank: calls are collective)
+};
+int cap_peer_alloc(struct cap_handle_s* h, struct cap_comm_s* comm, size_t bytes, cap_peer_s** out);   // collective
+int cap_peer_free(cap_peer_s* p);
+int cap_peer_free_collective(struct cap_handle_s* h, cap_peer_s* p);
+
 struct cap_handle_s {
   int device = 0;
   int num_sms = 148;
@@ -28,7 +43,19 @@ struct cap_handle_s {
   cudaEvent_t ev_trmm = nullptr, ev_gath[2] = {nullptr, nullptr}, ev_u2 = nullptr;
   struct cap_comm_s* dup_comm = nullptr;     // duplicate of dup_parent for those all-gathers (owned by the handle)
   struct cap_comm_s* dup_parent = nullptr;
-  int lookahead_pipeline = -1;        // -1 = by rank count (measured: 1 on one rank, 0 on several), 0 / 1 forced
+  int lookahead_pipeline = -1;        // -1 = the asynchronous schedule (potrf_1d.cuh), 0 / 1 = round-1 two-stream / pipelined NCCL orders
+  // asynchronous look-ahead Cholesky (potrf_1d.cuh): ring of events, exchange / signal streams, peer-mapped landing buffers
+  enum { RING = 4 };
+  cudaStream_t xchg_stream = nullptr, sig_stream = nullptr;
+  cudaEvent_t ev_leaf[RING] = {}, ev_csolve[RING] = {}, ev_solve[RING] = {}, ev_xchg[RING] = {}, ev_xpush[RING] = {}, ev_r1[RING] = {}, ev_r2a[RING] = {}, ev_r2[RING] = {};
+  cap_peer_s* peer1d = nullptr;       // landing buffers of the panel exchange (owned)
+  int peer_exchange = -1;             // -1 = peer copy engines when CUDA IPC works, else NCCL; 0 = NCCL orders of round 1; 1 = required
+  void* fn_wait32 = nullptr;          // cuStreamWaitValue32 / cuStreamWriteValue32 (driver entry points)
+  void* fn_write32 = nullptr;
+  uint32_t* sig_scratch = nullptr;    // one word per signalling stream: the value a 4-byte peer copy carries
+  struct cap_comm_s* peer_failed_comm = nullptr;   // CUDA IPC mapping failed on this communicator: do not retry every call
+  int lookahead_grid_mult = 0;        // tile-engine grid multiplier of the trailing update beside a chain (0 = keep the persistent grid)
+  int grid_mult = 1;                  // tile engine: CTAs per SM worth of grid (1 = persistent, one CTA per SM)
   int ws_bank = 0;                    // which split-K workspace slot gemm launches use (1 while launching on the panel stream)
   int lookahead_reserve_sms = 16;     // SMs the trailing update leaves free while a panel runs beside it
   int potrf_schedule = 0;             // cap_dpotrf on more than one block: 0 = right-looking with look-ahead, 1 = recursive

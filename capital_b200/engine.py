@@ -107,6 +107,14 @@ class Engine:
     def set_lookahead(self, reserve_sms=16, pipeline=-1):
         _lib.check(self.lib.cap_set_lookahead(self.h, int(reserve_sms), int(pipeline)), "cap_set_lookahead")
 
+    def set_peer_exchange(self, mode=-1):
+        """Panel exchange of potrf_1d: -1 = peer copy engines when CUDA IPC works, 0 = NCCL only, 1 = peer copy engines required."""
+        _lib.check(self.lib.cap_set_peer_exchange(self.h, int(mode)), "cap_set_peer_exchange")
+
+    def set_update_grid(self, ctas_per_sm=0):
+        """Trailing update beside a chain: 0 = persistent SM-capped grid, k > 0 = k x #SMs CTAs without a cap."""
+        _lib.check(self.lib.cap_set_update_grid(self.h, int(ctas_per_sm)), "cap_set_update_grid")
+
     def set_potrf_schedule(self, schedule):
         """0 = right-looking with look-ahead (cap_potrf_1d on one rank), 1 = recursive potrf / trsm / syrk."""
         _lib.check(self.lib.cap_set_potrf_schedule(self.h, int(schedule)), "cap_set_potrf_schedule")

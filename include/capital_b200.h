@@ -160,12 +160,20 @@ int cap_cholinv_factor(cap_handle_t h, cap_grid_t grid, int64_t n_loc, double* A
 int cap_potrf_1d(cap_handle_t h, cap_comm_t comm, int64_t N, int nb, double* A_loc, int64_t lda);
 int cap_potrf_1d_layout(int64_t N, int nb, int nranks, int rank, int64_t* ncols_loc, int* nblocks_loc);
 int cap_potrf_1d_block(int64_t j, int nranks, int* owner, int* local_block);
-/* reserve_sms: SMs the trailing update leaves to the concurrently running panel (default 16; 0 = no reservation).
- * pipeline: 1 = the row-panel all-gather runs on its own stream and a duplicate communicator, off the diagonal-block
- * chain; 0 = panel operations and all-gather in one stream; -1 (default) = 1 on one rank, 0 on several (what measured
- * fastest on 1, 2 and 8 B200).  NOTE: with pipeline = 1 on several ranks the handle keeps a duplicate of comm; destroy
- * the handle before the communicator it was used with. */
+/* reserve_sms: SMs the trailing update leaves to a diagonal-block chain running beside it (default 16; 0 = none).
+ * pipeline: -1 (default) = the asynchronous schedule: the chain leaf -> X -> next diagonal block runs two panels ahead of
+ * the trailing update on its owner, and between ranks every solved block is written into the peers' row-panel buffers by
+ * the copy engines over NVSwitch (CUDA-IPC peer memory, stream memory-op flags; no NCCL kernel on any SM).  Falls back to
+ * order 0 when CUDA IPC is not available between the ranks.  0 / 1 = the round-1 orders over NCCL (panel operations and
+ * all-gather in one stream / the all-gather on its own stream and a duplicate communicator).
+ * NOTE: the handle keeps peer mappings (and with pipeline = 1 a duplicate of comm): destroy the handle before the
+ * communicator it was used with. */
 int cap_set_lookahead(cap_handle_t h, int reserve_sms, int pipeline);
+/* panel exchange of cap_potrf_1d: -1 (default) = peer copy engines when CUDA IPC works, else NCCL; 0 = NCCL only; 1 = required */
+int cap_set_peer_exchange(cap_handle_t h, int mode);
+/* tile-engine grid of the trailing update that runs beside a chain: 0 (default) = persistent, one CTA per SM, SM-capped by
+ * reserve_sms; k > 0 = k x #SMs CTAs, no cap (high-priority chain kernels then get an SM at the next tile boundary) */
+int cap_set_update_grid(cap_handle_t h, int ctas_per_sm);
 /* cap_dpotrf on more than one potrf_nb block: 0 (default) = cap_potrf_1d on one rank, 1 = recursive potrf / trsm / syrk */
 int cap_set_potrf_schedule(cap_handle_t h, int schedule);
 

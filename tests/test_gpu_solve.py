@@ -124,8 +124,8 @@ def test_trtri_batched_leaves_vs_numpy(engine, uplo, n):
     assert np.array_equal(other, np.tril(stored, -1) if uplo == "U" else np.triu(stored, 1))
 
 
-@pytest.mark.parametrize("pipeline", [0, 1])
-@pytest.mark.parametrize("n,nb,reserve", [(100, 128, 16), (640, 128, 16), (1000, 256, 0), (1300, 256, 16), (2500, 512, 16), (4096, 1024, 8)])
+@pytest.mark.parametrize("pipeline", [-1, 0, 1])
+@pytest.mark.parametrize("n,nb,reserve", [(100, 128, 16), (640, 128, 16), (1000, 256, 0), (1300, 256, 16), (2500, 512, 16), (4096, 1024, 8), (1536, 128, 16)])
 def test_potrf_lookahead_one_rank_vs_numpy(blocks, n, nb, reserve, pipeline):
     """cap_potrf_1d on one rank = cap_dpotrf with schedule 0: right-looking, panel(j+1) beside the trailing update of j."""
     from capital_b200.engine import colmajor
@@ -165,7 +165,8 @@ def test_potrf_lookahead_info(blocks):
         eng.set_potrf_schedule(0)
 
 
-@pytest.mark.parametrize("world,n,nb,pipeline", [(2, 1500, 256, 1), (2, 4096, 512, 0), (4, 3000, 256, 1), (8, 4096, 256, 1)])
+@pytest.mark.parametrize("world,n,nb,pipeline", [(2, 1500, 256, 1), (2, 4096, 512, 0), (4, 3000, 256, 1), (8, 4096, 256, 1),
+                                                   (2, 1500, 256, -1), (2, 4096, 128, -1), (4, 3000, 256, -1), (8, 4096, 256, -1), (8, 4000, 128, -1)])
 def test_potrf_1d_multi_gpu(world, n, nb, pipeline):
     import os
     import subprocess

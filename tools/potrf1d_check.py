@@ -31,7 +31,9 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("N", type=int)
     ap.add_argument("nb", type=int, nargs="+")
-    ap.add_argument("--pipeline", type=int, nargs="+", default=[1])
+    ap.add_argument("--pipeline", type=int, nargs="+", default=[-1], help="-1 = asynchronous schedule (peer copy engines), 0 / 1 = round-1 NCCL orders")
+    ap.add_argument("--grid", type=int, nargs="+", default=[0], help="cap_set_update_grid values to time (0 = persistent SM-capped grid)")
+    ap.add_argument("--exchange", type=int, default=-1, help="cap_set_peer_exchange: -1 auto, 0 NCCL only, 1 peer required")
     ap.add_argument("--time", type=int, default=0)
     ap.add_argument("--reserve", type=int, nargs="+", default=[16])
     ap.add_argument("--no-check", action="store_true")
@@ -45,6 +47,7 @@ def main():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     eng = Engine(local)
+    eng.set_peer_exchange(args.exchange)
     comm = cdist.Comm(eng) if world > 1 else None
     cptr = comm.ptr if comm else None
     N = args.N
@@ -109,18 +112,19 @@ def main():
             t_copy = timed(lambda: A.copy_(A0))
             for pipeline in args.pipeline:
                 for reserve in args.reserve:
-                    eng.set_lookahead(reserve, pipeline)
+                  for grid in args.grid:
+                    eng.set_lookahead(reserve, pipeline); eng.set_update_grid(grid)
                     for _ in range(2):
                         A.copy_(A0); eng.potrf_1d(A, N, nb, cptr)
                     t = timed(lambda: (A.copy_(A0), eng.potrf_1d(A, N, nb, cptr))) - t_copy
                     tf = N ** 3 / 3 / t * 1e-9
                     good, worst = check()
                     all_ok = all_ok and good
-                    results.append({"N": N, "nb": nb, "gpus": world, "reserve_sms": reserve, "pipeline": pipeline, "ms": t, "tflops": tf,
+                    results.append({"N": N, "nb": nb, "gpus": world, "reserve_sms": reserve, "pipeline": pipeline, "update_grid": grid, "ms": t, "tflops": tf,
                                     "frac_of_peak": tf / (PEAK * world), "rel_vs_reference": worst, "ok": bool(good)})
                     if rank == 0:
-                        print("potrf_1d N=%d nb=%d on %d GPU(s), pipeline %d, %d SMs reserved: %.3f ms  %.2f TFLOP/s  %.1f %% of %d x %.1f  (rank 0: rel %.1e %s)" % (
-                            N, nb, world, pipeline, reserve, t, tf, 100 * tf / (PEAK * world), world, PEAK, worst, "OK" if good else "FAIL"), flush=True)
+                        print("potrf_1d N=%d nb=%d on %d GPU(s), pipeline %d, %d SMs reserved, grid x%d: %.3f ms  %.2f TFLOP/s  %.1f %% of %d x %.1f  (rank 0: rel %.1e %s)" % (
+                            N, nb, world, pipeline, reserve, grid, t, tf, 100 * tf / (PEAK * world), world, PEAK, worst, "OK" if good else "FAIL"), flush=True)
         if args.timeline:
             for _ in range(2):
                 A.copy_(A0); eng.potrf_1d(A, N, nb, cptr)
