@@ -50,6 +50,7 @@ int cap_create(cap_handle_t* out, int device) {
   cap_handle_s* h = new cap_handle_s();
   h->device = device;
   h->num_sms = prop.multiProcessorCount;
+  if (const char* e = getenv("CAPITAL_B200_STAIR")) h->lookahead_stair = atoi(e);     // A/B switch: 0 = trailing update block run by block run
   CUDA_TRY(cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking));
   CUDA_TRY(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
   h->stream = h->own_stream;
@@ -296,6 +297,43 @@ static int gemm_launch(cap_handle_t h, GemmParams p, bool ta, bool tb, int want_
     splitk_reduce_kernel<<<rg, 128, 0, h->stream>>>(p.C, p.c_split_stride, p.M, ksplit, user_c, user_ldc, p.M, p.N, alpha, beta, p.c_tri);
     LAUNCH_CHECK(h);
   }
+  return CAP_OK;
+}
+
+// One launch for the whole trailing update of a rank in the 1-D look-ahead Cholesky (SCHED_STAIR, dmma_tma_gemm.cuh):
+// C[:, local blocks r_first ..] (rows from global block row0) += alpha * A^T B on and above the global diagonal.
+// A: K x M (the ordered row panel from block row0 on), B: K x N (this rank's solved blocks), both k-contiguous.
+// Returns CAP_ERR_UNSUPPORTED when the operands do not meet TMA's alignment rules (the caller then goes block by block).
+static int stair_launch(cap_handle_t h, const double* A, int64_t lda, const double* B, int64_t ldb, double* C, int64_t ldc,
+                        int64_t M, int64_t N, int K, double alpha, int nb, int P, int me, int r_first, int row0) {
+  if (M <= 0 || N <= 0) return CAP_OK;
+  GemmParams g{}; g.A = A; g.B = B; g.lda = lda; g.ldb = ldb; g.K = K;
+  if (!tma_eligible(h, g)) return CAP_ERR_UNSUPPORTED;
+  TmaGemmParams tp{};
+  tp.C = C; tp.Cin = C; tp.ldc = ldc; tp.ldcin = ldc; tp.M = (int)M; tp.N = (int)N; tp.K = K; tp.alpha = alpha; tp.beta = 1.0;
+  tp.c_tri = CTRI_UPPER; tp.diag = DIAG_NONE; tp.ksplit = 1; tp.k_per_split = K;
+  tp.tiles_m = (int)((M + BM - 1) / BM); tp.tiles_n = (int)((N + BN - 1) / BN);
+  tp.sched = SCHED_STAIR; tp.subs = 1;
+  tp.stair_T = nb / BM; tp.stair_P = P; tp.stair_me = me; tp.stair_r_first = r_first; tp.stair_row0 = row0;
+  int64_t units = 0;
+  const int T = tp.stair_T;
+  for (int bi = 0; bi * T < tp.tiles_n; ++bi) {
+    const int rb = r_first + bi;
+    const int gblk = rb * P + ((rb & 1) ? P - 1 - me : me);
+    const int Tb = std::min(T, tp.tiles_n - bi * T);
+    const int base = (gblk - row0) * T + 1;
+    if (base < 1) return cap_fail(CAP_ERR_ARG, "stair_launch", "block column left of the first row block");
+    units += (int64_t)Tb * base + (int64_t)Tb * (Tb - 1) / 2;
+  }
+  if (units > INT32_MAX) return cap_fail(CAP_ERR_ARG, "stair_launch", "too many tiles");
+  tp.units = (int)units;
+  tp.c_vec2 = aligned16(C, ldc) ? 1 : 0;
+  CUtensorMap ma, mb;
+  CAP_TRY(make_map(h, &ma, A, K, M, lda, true));
+  CAP_TRY(make_map(h, &mb, B, K, N, ldb, true));
+  const int grid = (int)std::min<int64_t>(tp.units, (int64_t)h->num_sms * std::max(1, h->grid_mult));
+  launch_tma_t<true, true>(h, ma, mb, tp, grid);
+  LAUNCH_CHECK(h);
   return CAP_OK;
 }
 

@@ -5,7 +5,10 @@
 #include "handle.h"
 
 #include <nccl.h>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
+#include <string>
 #include <vector>
 
 struct cap_comm_s {
@@ -101,10 +104,14 @@ int cap_peer_alloc(cap_handle_s* h, cap_comm_s* comm, size_t bytes, cap_peer_s**
   p->rank = me; p->size = P; p->bytes = bytes; p->comm = comm;
   int bad = 0;
   void* local = nullptr;
-  if (cudaMalloc(&local, bytes) != cudaSuccess) { cudaGetLastError(); bad = 1; }
+  std::string why;
+  auto note = [&](const char* step, cudaError_t e) { why = std::string(step) + ": " + cudaGetErrorString(e); cudaGetLastError(); bad = 1; };
+  cudaError_t ce;
+  if ((ce = cudaMalloc(&local, bytes)) != cudaSuccess) note("cudaMalloc", ce);
   cudaIpcMemHandle_t mine;
   memset(&mine, 0, sizeof(mine));
-  if (!bad && (cudaMemset(local, 0, bytes) != cudaSuccess || cudaIpcGetMemHandle(&mine, local) != cudaSuccess)) { cudaGetLastError(); bad = 1; }
+  if (!bad && (ce = cudaMemset(local, 0, bytes)) != cudaSuccess) note("cudaMemset", ce);
+  if (!bad && (ce = cudaIpcGetMemHandle(&mine, local)) != cudaSuccess) note("cudaIpcGetMemHandle", ce);
   static_assert(sizeof(cudaIpcMemHandle_t) == 64, "CUDA IPC handles are 64 bytes");
   char* stage = nullptr;                                   // [P handles][P status words]
   const size_t hb = sizeof(cudaIpcMemHandle_t);
@@ -119,7 +126,7 @@ int cap_peer_alloc(cap_handle_s* h, cap_comm_s* comm, size_t bytes, cap_peer_s**
   for (int r = 0; r < P && !bad; ++r) {
     if (r == me) continue;
     void* q = nullptr;
-    if (cudaIpcOpenMemHandle(&q, all[r], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); bad = 1; break; }
+    if ((ce = cudaIpcOpenMemHandle(&q, all[r], cudaIpcMemLazyEnablePeerAccess)) != cudaSuccess) { note("cudaIpcOpenMemHandle", ce); break; }
     p->ptr[r] = (char*)q;
   }
   // agree on the outcome: sum of the per-rank failure flags
@@ -132,7 +139,8 @@ int cap_peer_alloc(cap_handle_s* h, cap_comm_s* comm, size_t bytes, cap_peer_s**
   cudaFree(stage);
   if (nr != ncclSuccess || total != 0.f) {
     cap_peer_free(p);
-    return cap_fail(CAP_ERR_UNSUPPORTED, "cap_peer_alloc", "CUDA IPC peer mapping is not available between these ranks");
+    if (getenv("CAPITAL_B200_VERBOSE") || bad) fprintf(stderr, "[capital_b200] rank %d: peer mapping of %zu bytes unavailable (%s); NCCL exchange is used instead\n", me, bytes, bad ? why.c_str() : "another rank failed");
+    return cap_fail(CAP_ERR_UNSUPPORTED, "cap_peer_alloc", bad ? why.c_str() : "CUDA IPC peer mapping failed on another rank");
   }
   *out = p;
   return CAP_OK;

@@ -40,7 +40,7 @@ constexpr int T_THREADS = (T_CONSUMER_WARPS + 4) * 32;  // + one producer warpgr
 constexpr int T_REGS_CONSUMER = 240, T_REGS_PRODUCER = 24;
 constexpr int T_SMEM_BYTES = T_STAGES * T_STAGE_BYTES + 1024 /*alignment slack*/ + 256 /*mbarriers*/;
 
-enum : int { SCHED_RASTER = 0, SCHED_TRI = 1, SCHED_ROWPANEL_DESC = 2, SCHED_ROWPANEL_ASC = 3, SCHED_TM_DESC = 4 };
+enum : int { SCHED_RASTER = 0, SCHED_TRI = 1, SCHED_ROWPANEL_DESC = 2, SCHED_ROWPANEL_ASC = 3, SCHED_TM_DESC = 4, SCHED_STAIR = 5 };
 // which operand is triangular on the diagonal k-block (the relation that holds for NON-zero entries)
 enum : int { DIAG_NONE = 0, DIAG_A_LE = 1 /* r <= k */, DIAG_A_GE = 2 /* r >= k */, DIAG_B_LE = 3 /* k <= c */, DIAG_B_GE = 4 /* k >= c */ };
 
@@ -58,6 +58,9 @@ struct TmaGemmParams {
   int sched;
   int units, subs;          // persistent loop: unit = blockIdx.x + i*gridDim.x, `subs` tiles per unit
   int c_vec2;               // C/Cin 16-byte aligned with even ld: paired-row stores allowed
+  // SCHED_STAIR: C is a run of block columns of a 1-D block-cyclic (boustrophedon) matrix, rows start at global block
+  // stair_row0; only tiles on or above the GLOBAL diagonal exist (one launch = the whole trailing update of a rank)
+  int stair_T, stair_P, stair_me, stair_r_first, stair_row0;   // tiles per block, ranks, this rank, first local block, first row block
 };
 
 // ------------------------------------------------------------------------------------------ PTX wrappers
@@ -91,7 +94,7 @@ __device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* m
 // stage kt of a tile covers k0 = k_first + kt*k_step .. k0+15 (k_step = +-16: row-panel schedules walk k in
 // alternating directions so that a panel block is re-read while it is still in L2); the diagonal 128-block
 // of a triangular operand starts at k = diag_origin.
-struct TileInfo { int tm, tn, kz, k_first, k_step, nk, diag_origin; };
+struct TileInfo { int tm, tn, kz, k_first, k_step, nk, diag_origin; bool tri_diag; };
 struct TrueTag { static constexpr bool value = true; };
 struct FalseTag { static constexpr bool value = false; };
 
@@ -99,6 +102,27 @@ __device__ __forceinline__ TileInfo decode_tile(const TmaGemmParams& p, int unit
   TileInfo t;
   int tile = unit;
   t.kz = 0;
+  t.tri_diag = false;
+  if (p.sched == SCHED_STAIR) {
+    // column-major walk over the tiles of every block column that lie on or above the global diagonal: the column tile
+    // `ct` of local block rb (global block g) has (g - row0) * T + ct + 1 row tiles, the last of which is triangular
+    const int T = p.stair_T;
+    int rem = unit;
+    for (int bi = 0;; ++bi) {
+      const int rb = p.stair_r_first + bi;
+      const int g = rb * p.stair_P + ((rb & 1) ? p.stair_P - 1 - p.stair_me : p.stair_me);
+      const int Tb = min(T, p.tiles_n - bi * T);
+      const int base = (g - p.stair_row0) * T + 1;
+      const int cnt = Tb * base + Tb * (Tb - 1) / 2;
+      if (rem < cnt || (bi + 1) * T >= p.tiles_n) {
+        int ct = 0;
+        while (ct + 1 < Tb && rem >= base + ct) { rem -= base + ct; ++ct; }
+        t.tn = bi * T + ct; t.tm = rem; t.tri_diag = (rem == base + ct - 1);
+        break;
+      }
+      rem -= cnt;
+    }
+  } else
   if (p.sched == SCHED_ROWPANEL_DESC) { t.tm = unit; t.tn = p.tiles_n - 1 - sub; }
   else if (p.sched == SCHED_ROWPANEL_ASC) { t.tm = unit; t.tn = sub; }
   else {
@@ -132,11 +156,13 @@ __device__ __forceinline__ TileInfo decode_tile(const TmaGemmParams& p, int unit
   t.k_step = descending ? -BK : BK;
   t.k_first = descending ? k_begin + (t.nk - 1) * BK : k_begin;
   t.diag_origin = (p.diag == DIAG_A_LE || p.diag == DIAG_A_GE) ? m0 : n0;
+  if (p.sched != SCHED_STAIR) t.tri_diag = (p.c_tri != CTRI_FULL && t.tm == t.tn);
   return t;
 }
 
 // skip tiles entirely outside the stored triangle of C (only reachable with the rectangular raster)
 __device__ __forceinline__ bool tile_outside_tri(const TmaGemmParams& p, const TileInfo& t) {
+  if (p.sched == SCHED_STAIR) return false;
   if (p.c_tri == CTRI_UPPER && t.tn * BN + BN - 1 < t.tm * BM) return true;
   if (p.c_tri == CTRI_LOWER && t.tm * BM + BM - 1 < t.tn * BN) return true;
   return false;
@@ -363,7 +389,7 @@ __device__ __forceinline__ void store_tile(const TmaGemmParams& p, const TileInf
   double alpha = p.alpha, beta = p.beta;
   if (p.ksplit > 1) { C += (int64_t)ti.kz * p.c_split_stride; alpha = 1.0; beta = 0.0; }
   const int m0 = ti.tm * BM, n0 = ti.tn * BN;
-  const bool full = (m0 + BM <= p.M) && (n0 + BN <= p.N) && (p.c_tri == CTRI_FULL || ti.tm != ti.tn);
+  const bool full = (m0 + BM <= p.M) && (n0 + BN <= p.N) && !ti.tri_diag;
   if (!A_KC && p.c_vec2 && full) {
     // row tiles 2j and 2j+1 hold rows 16j+2g and 16j+2g+1: one 16-byte store per pair
 #pragma unroll
@@ -394,8 +420,8 @@ __device__ __forceinline__ void store_tile(const TmaGemmParams& p, const TileInf
       for (int e = 0; e < 2; ++e) {
         const int c = n0 + acc_col<B_KC>(wn, jj, 2 * t + e);
         if (c >= p.N) continue;
-        if (p.c_tri == CTRI_UPPER && r > c) continue;
-        if (p.c_tri == CTRI_LOWER && r < c) continue;
+        if (ti.tri_diag && p.c_tri == CTRI_UPPER && r - m0 > c - n0) continue;     // (a triangular C crosses a tile only where
+        if (ti.tri_diag && p.c_tri == CTRI_LOWER && r - m0 < c - n0) continue;     //  its row and column origins coincide)
         double v = alpha * acc[i][jj][e];
         if (beta != 0.0) v += beta * p.Cin[r + (int64_t)c * p.ldcin];
         C[r + (int64_t)c * p.ldc] = v;
@@ -473,7 +499,7 @@ dmma_tma_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_cons
       for (int i = 0; i < 8; ++i)
 #pragma unroll
         for (int jj = 0; jj < 4; ++jj) acc[i][jj][0] = acc[i][jj][1] = 0.0;
-      const uint32_t tile_mask = (p.c_tri != CTRI_FULL && ti.tm == ti.tn) ? ctri_mask(p.c_tri, wm, wn) : 0xFFu;
+      const uint32_t tile_mask = ti.tri_diag ? ctri_mask(p.c_tri, wm, wn) : 0xFFu;
       // software pipeline in quarter stages (half of the k-columns x half of the rows): the next quarter's
       // fragments are in flight while the DMMAs of the current one issue (the 8 warps run in lockstep, so
       // un-overlapped LDS bursts would idle the pipe)

@@ -55,6 +55,7 @@ struct cap_handle_s {
   uint32_t* sig_scratch = nullptr;    // one word per signalling stream: the value a 4-byte peer copy carries
   struct cap_comm_s* peer_failed_comm = nullptr;   // CUDA IPC mapping failed on this communicator: do not retry every call
   int lookahead_grid_mult = 0;        // tile-engine grid multiplier of the trailing update beside a chain (0 = keep the persistent grid)
+  int lookahead_stair = 1;            // trailing update of the asynchronous schedule as ONE staircase launch (0 = a gemm + a syrk per run of blocks)
   int grid_mult = 1;                  // tile engine: CTAs per SM worth of grid (1 = persistent, one CTA per SM)
   int ws_bank = 0;                    // which split-K workspace slot gemm launches use (1 while launching on the panel stream)
   int lookahead_reserve_sms = 16;     // SMs the trailing update leaves free while a panel runs beside it

@@ -370,7 +370,7 @@ struct Async1D {
   int signal(cudaStream_t s, int slot, int q, size_t off, uint32_t value) {
     const CUresult r = ((stream_value32_fn)h->fn_write32)((CUstream)s, (CUdeviceptr)(h->sig_scratch + slot), value, CU_STREAM_WRITE_VALUE_DEFAULT);
     if (r != CUDA_SUCCESS) return cap_fail(CAP_ERR_CUDA, "cuStreamWriteValue32", "failed");
-    CUDA_TRY(cudaMemcpyAsync(peer->ptr[q] + off, h->sig_scratch + slot, sizeof(uint32_t), cudaMemcpyDeviceToDevice, s));
+    CUDA_TRY(cudaMemcpyAsync(peer->ptr[q] + off, h->sig_scratch + slot, sizeof(uint32_t), cudaMemcpyDefault, s));
     return CAP_OK;
   }
 
@@ -418,7 +418,7 @@ struct Async1D {
       const int q = (first + i) % L.P;
       if (q == me) continue;
       CAP_TRY(wait_flag(sx, off_ack + (size_t)q * 4, ack_needed(k)));
-      CUDA_TRY(cudaMemcpyAsync(peer->ptr[q] + off_X[b], X[b], (size_t)nb * nb * 8, cudaMemcpyDeviceToDevice, sx));
+      CUDA_TRY(cudaMemcpyAsync(peer->ptr[q] + off_X[b], X[b], (size_t)nb * nb * 8, cudaMemcpyDefault, sx));
       CAP_TRY(signal(sx, 1, q, off_flag_x + (size_t)b * 4, seq(k)));
     }
     CUDA_TRY(cudaEventRecord(h->ev_xpush[b], sx));
@@ -469,7 +469,7 @@ struct Async1D {
         for (int r = r0; r < n; ++r) {
           const int l = L.global_block(r, me);
           CUDA_TRY(cudaMemcpyAsync(peer->ptr[q] + off_R[b] + (size_t)(l - j - 1) * nb * nb * 8, S[b] + (int64_t)(r - r0) * nb * nb,
-                                   (size_t)nb * L.width(l) * 8, cudaMemcpyDeviceToDevice, sc));
+                                   (size_t)nb * L.width(l) * 8, cudaMemcpyDefault, sc));
         }
         CAP_TRY(signal(sc, 0, q, off_flag_r + ((size_t)me * RING + b) * 4, seq(j)));
       }
@@ -507,6 +507,15 @@ struct Async1D {
     const int r0 = r0_of(j);
     int r = r0;
     while (r < n && L.global_block(r, me) < j + 3) ++r;
+    if (r >= n) return CAP_OK;
+    if (h->lookahead_stair) {
+      // ONE launch: every tile of this rank's block columns on or above the global diagonal (no per-run tails, no 36-tile syrk launches)
+      const int g_last = L.global_block(n - 1, me);
+      const int64_t rows = std::min<int64_t>(L.N, (int64_t)(g_last + 1) * nb) - (int64_t)(j + 2) * nb;
+      const int rc = stair_launch(h, R[b] + (int64_t)nb * nb, nb, S[b] + (int64_t)(r - r0) * nb * nb, nb, blockptr(j + 2, r), lda,
+                                  rows, cols_from(r), nb, -1.0, nb, L.P, me, r, j + 2);
+      if (rc != CAP_ERR_UNSUPPORTED) return rc;
+    }
     while (r < n) {
       int r_end = r + 1;                                          // run of consecutive global blocks [k0, k1]
       while (r_end < n && L.global_block(r_end, me) == L.global_block(r_end - 1, me) + 1) ++r_end;
@@ -530,10 +539,13 @@ struct Async1D {
     }
     if (nblk > 1) CAP_TRY(chain_front(1));            // before solve_rest(0): its events are waited on by the exchange of panel 0
     { StreamScope scope(h, sm, 0); CAP_TRY(solve_rest(0)); }
+    // SMs left to the chain: only while a chain runs on THIS rank beside the work being launched
+    auto reserve_for = [&](int k) { return (k < nblk && (L.P == 1 || me == L.owner(k)) && h->lookahead_reserve_sms > 0) ? h->num_sms - h->lookahead_reserve_sms : 0; };
     for (int j = 0; j + 1 < nblk; ++j) {
       const int b = j % RING;
       {
         StreamScope scope(h, sm, 0);
+        SmCapScope cap(h, reserve_for(j + 1));         // leaf(j+1) may still be running here
         CAP_TRY(row_data_ready(j));
         tl.mark(sm, j, "U1");
         CAP_TRY(update_row(j));
@@ -545,10 +557,9 @@ struct Async1D {
       if (j + 2 < nblk) CAP_TRY(chain_front(j + 2));
       {
         StreamScope scope(h, sm, 0);
+        SmCapScope cap(h, reserve_for(j + 2));         // the chain of panel j+2 runs beside the rest of this iteration
         CAP_TRY(solve_rest(j + 1));
         if (j + 2 < nblk) {
-          const bool chain_beside = (L.P == 1 || me == L.owner(j + 2));
-          SmCapScope cap(h, (chain_beside && h->lookahead_reserve_sms > 0) ? h->num_sms - h->lookahead_reserve_sms : 0);
           GridMultScope gm(h, h->lookahead_grid_mult);
           tl.mark(sm, j, "U2");
           CAP_TRY(update_rest(j));
@@ -588,7 +599,7 @@ static int async_streams(cap_handle_t h) {
     cudaDriverEntryPointQueryResult qres;
     void* fn = nullptr;
     if (cudaGetDriverEntryPoint(name, &fn, cudaEnableDefault, &qres) != cudaSuccess || qres != cudaDriverEntryPointSuccess || !fn) { cudaGetLastError(); fn = nullptr; }
-    (name[8] == 'a' ? h->fn_wait32 : h->fn_write32) = fn;      // cuStreamW[a]it / cuStreamW[r]ite
+    (name[9] == 'a' ? h->fn_wait32 : h->fn_write32) = fn;      // cuStreamWa.. / cuStreamWr..
   }
   return CAP_OK;
 }
@@ -596,7 +607,9 @@ static int async_streams(cap_handle_t h) {
 // Landing buffers of the exchange: one symmetric allocation per handle, re-made (collectively) when a call needs more.
 static int async_peer(cap_handle_t h, cap_comm_t comm, size_t bytes, cap_peer_s** out) {
   *out = nullptr;
-  if (h->peer_exchange == 0 || !h->fn_wait32 || !h->fn_write32) return CAP_OK;
+  if (h->peer_exchange == 0) return CAP_OK;
+  if (!h->fn_wait32 || !h->fn_write32)
+    return h->peer_exchange == 1 ? cap_fail(CAP_ERR_UNSUPPORTED, "cap_potrf_1d", "cuStreamWaitValue32 / cuStreamWriteValue32 are not available from this driver") : CAP_OK;
   if (h->peer1d && (h->peer1d->comm != comm || h->peer1d->bytes < bytes)) { CAP_TRY(cap_peer_free_collective(h, h->peer1d)); h->peer1d = nullptr; }
   if (!h->peer1d) {
     if (h->peer_failed_comm == comm) return CAP_OK;                 // tried before on this communicator: CUDA IPC is not available
