@@ -50,6 +50,7 @@ int cap_create(cap_handle_t* out, int device) {
   cap_handle_s* h = new cap_handle_s();
   h->device = device;
   h->num_sms = prop.multiProcessorCount;
+  if (const char* e = getenv("CAPITAL_B200_GRID_MULT")) h->grid_mult = std::max(1, atoi(e));   // probe switch: tile-engine grid = k x #SMs everywhere
   if (const char* e = getenv("CAPITAL_B200_STAIR")) h->lookahead_stair = atoi(e);     // A/B switch: 0 = trailing update block run by block run
   CUDA_TRY(cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking));
   CUDA_TRY(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
@@ -105,9 +106,9 @@ int cap_destroy(cap_handle_t h) {
     for (cudaEvent_t e : {h->ev_panel[0], h->ev_panel[1], h->ev_u1, h->ev_trmm, h->ev_gath[0], h->ev_gath[1], h->ev_u2}) cudaEventDestroy(e);
   }
   if (h->xchg_stream) {
-    cudaStreamDestroy(h->xchg_stream); cudaStreamDestroy(h->sig_stream);
+    cudaStreamDestroy(h->xchg_stream); cudaStreamDestroy(h->sig_stream); cudaStreamDestroy(h->row_stream);
     for (int i = 0; i < cap_handle_s::RING; ++i)
-      for (cudaEvent_t e : {h->ev_leaf[i], h->ev_csolve[i], h->ev_solve[i], h->ev_xchg[i], h->ev_xpush[i], h->ev_r1[i], h->ev_r2a[i], h->ev_r2[i]}) cudaEventDestroy(e);
+      for (cudaEvent_t e : {h->ev_leaf[i], h->ev_csolve[i], h->ev_solve[i], h->ev_xchg[i], h->ev_xpush[i], h->ev_rowready[i], h->ev_r1[i], h->ev_r2a[i], h->ev_r2[i]}) cudaEventDestroy(e);
     cudaFree(h->sig_scratch);
   }
   if (h->peer1d) { cudaDeviceSynchronize(); cap_peer_free(h->peer1d); h->peer1d = nullptr; }
@@ -248,7 +249,7 @@ static int gemm_launch(cap_handle_t h, GemmParams p, bool ta, bool tb, int want_
     ksplit = (p.K + kper - 1) / kper;
     if (ksplit > 1) {
       double* part;
-      CAP_TRY(cap_workspace(h, h->ws_bank ? CAP_WS_GEMM_SPLITK2 : CAP_WS_GEMM_SPLITK, (size_t)ksplit * p.M * p.N * sizeof(double), &part));
+      CAP_TRY(cap_workspace(h, h->ws_bank == 0 ? CAP_WS_GEMM_SPLITK : (h->ws_bank == 1 ? CAP_WS_GEMM_SPLITK2 : CAP_WS_GEMM_SPLITK3), (size_t)ksplit * p.M * p.N * sizeof(double), &part));
       p.k_per_split = kper; p.c_split_stride = (int64_t)p.M * p.N; p.C = part; p.ldc = p.M;
     }
   }

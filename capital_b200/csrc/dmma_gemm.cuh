@@ -203,22 +203,38 @@ __device__ __forceinline__ void gemm_tile(const GemmParams& p, double* smem, int
   double alpha = p.alpha, beta = p.beta;
   const double* Cin = p.Cin;
   if (p.ksplit > 1) { C += (int64_t)kz * p.c_split_stride; alpha = 1.0; beta = 0.0; }
+  // batches of two row tiles: every read of Cin is in flight before the first write (C may alias Cin, so element-by-element
+  // code makes each load wait for the store before it -- 64 dependent L2 round trips per thread)
 #pragma unroll
-  for (int i = 0; i < 8; ++i) {
-    const int r = m0 + wm * 64 + frag_pos<!TA>(i, g);
-    if (r >= p.M) continue;
+  for (int i0 = 0; i0 < 8; i0 += 2) {
+    double o[2][4][2];
+    uint32_t live = 0;
 #pragma unroll
-    for (int j = 0; j < 4; ++j)
+    for (int ii = 0; ii < 2; ++ii) {
+      const int r = m0 + wm * 64 + frag_pos<!TA>(i0 + ii, g);
 #pragma unroll
-      for (int e = 0; e < 2; ++e) {
-        const int c = n0 + wn * 32 + frag_pos<TB>(j, 2 * t + e);
-        if (c >= p.N) continue;
-        if (p.c_tri == CTRI_UPPER && r > c) continue;
-        if (p.c_tri == CTRI_LOWER && r < c) continue;
-        double v = alpha * acc[i][j][e];
-        if (beta != 0.0) v += beta * Cin[r + (int64_t)c * p.ldcin];
-        C[r + (int64_t)c * p.ldc] = v;
-      }
+      for (int j = 0; j < 4; ++j)
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          const int c = n0 + wn * 32 + frag_pos<TB>(j, 2 * t + e);
+          bool ok = (r < p.M) && (c < p.N);
+          if (p.c_tri == CTRI_UPPER && r > c) ok = false;
+          if (p.c_tri == CTRI_LOWER && r < c) ok = false;
+          live |= (ok ? 1u : 0u) << (ii * 8 + j * 2 + e);
+          o[ii][j][e] = (ok && beta != 0.0) ? Cin[r + (int64_t)c * p.ldcin] : 0.0;
+        }
+    }
+#pragma unroll
+    for (int ii = 0; ii < 2; ++ii) {
+      const int r = m0 + wm * 64 + frag_pos<!TA>(i0 + ii, g);
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          const int c = n0 + wn * 32 + frag_pos<TB>(j, 2 * t + e);
+          if ((live >> (ii * 8 + j * 2 + e)) & 1u) C[r + (int64_t)c * p.ldc] = fma(beta, o[ii][j][e], alpha * acc[i0 + ii][j][e]);
+        }
+    }
   }
 }
 

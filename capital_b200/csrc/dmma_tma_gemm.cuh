@@ -390,41 +390,60 @@ __device__ __forceinline__ void store_tile(const TmaGemmParams& p, const TileInf
   if (p.ksplit > 1) { C += (int64_t)ti.kz * p.c_split_stride; alpha = 1.0; beta = 0.0; }
   const int m0 = ti.tm * BM, n0 = ti.tn * BN;
   const bool full = (m0 + BM <= p.M) && (n0 + BN <= p.N) && !ti.tri_diag;
+  // C and Cin may be the same array, so the compiler has to keep every load of Cin in front of the store that follows it:
+  // written element by element, beta != 0 costs 64 (32 paired) dependent round trips to L2 per thread -- 32 us per tile,
+  // measured (profiles/r02_update_probe.txt: time = K x ideal + 0.9 ms per 4096-tile launch at every K).  Hence batches
+  // (8 elements; larger ones spill): all reads of a batch are in flight before its first write.
   if (!A_KC && p.c_vec2 && full) {
     // row tiles 2j and 2j+1 hold rows 16j+2g and 16j+2g+1: one 16-byte store per pair
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
       const int r = m0 + acc_row<false>(wm, 2 * j, g);
 #pragma unroll
-      for (int jj = 0; jj < 4; ++jj)
+      for (int jh = 0; jh < 4; jh += 2) {
+        double2 o[2][2];
+        if (beta != 0.0) {
 #pragma unroll
-        for (int e = 0; e < 2; ++e) {
-          const int c = n0 + acc_col<B_KC>(wn, jj, 2 * t + e);
-          double2 v = make_double2(alpha * acc[2 * j][jj][e], alpha * acc[2 * j + 1][jj][e]);
-          if (beta != 0.0) {
-            const double2 o = *reinterpret_cast<const double2*>(p.Cin + r + (int64_t)c * p.ldcin);
-            v.x += beta * o.x; v.y += beta * o.y;
-          }
-          *reinterpret_cast<double2*>(C + r + (int64_t)c * p.ldc) = v;
+          for (int jj = 0; jj < 2; ++jj)
+#pragma unroll
+            for (int e = 0; e < 2; ++e)
+              o[jj][e] = *reinterpret_cast<const double2*>(p.Cin + r + (int64_t)(n0 + acc_col<B_KC>(wn, jh + jj, 2 * t + e)) * p.ldcin);
         }
+#pragma unroll
+        for (int jj = 0; jj < 2; ++jj)
+#pragma unroll
+          for (int e = 0; e < 2; ++e) {
+            const int c = n0 + acc_col<B_KC>(wn, jh + jj, 2 * t + e);
+            double2 v = make_double2(alpha * acc[2 * j][jh + jj][e], alpha * acc[2 * j + 1][jh + jj][e]);
+            if (beta != 0.0) { v.x += beta * o[jj][e].x; v.y += beta * o[jj][e].y; }
+            *reinterpret_cast<double2*>(C + r + (int64_t)c * p.ldc) = v;
+          }
+      }
     }
     return;
   }
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
     const int r = m0 + acc_row<A_KC>(wm, i, g);
-    if (r >= p.M) continue;
+    double o[4][2];
+    uint32_t live = 0;                       // bit (jj*2 + e): the element exists and is stored
 #pragma unroll
     for (int jj = 0; jj < 4; ++jj)
 #pragma unroll
       for (int e = 0; e < 2; ++e) {
         const int c = n0 + acc_col<B_KC>(wn, jj, 2 * t + e);
-        if (c >= p.N) continue;
-        if (ti.tri_diag && p.c_tri == CTRI_UPPER && r - m0 > c - n0) continue;     // (a triangular C crosses a tile only where
-        if (ti.tri_diag && p.c_tri == CTRI_LOWER && r - m0 < c - n0) continue;     //  its row and column origins coincide)
-        double v = alpha * acc[i][jj][e];
-        if (beta != 0.0) v += beta * p.Cin[r + (int64_t)c * p.ldcin];
-        C[r + (int64_t)c * p.ldc] = v;
+        bool ok = (r < p.M) && (c < p.N);
+        if (ti.tri_diag && p.c_tri == CTRI_UPPER && r - m0 > c - n0) ok = false;     // (a triangular C crosses a tile only where
+        if (ti.tri_diag && p.c_tri == CTRI_LOWER && r - m0 < c - n0) ok = false;     //  its row and column origins coincide)
+        live |= (ok ? 1u : 0u) << (jj * 2 + e);
+        o[jj][e] = (ok && beta != 0.0) ? p.Cin[r + (int64_t)c * p.ldcin] : 0.0;
+      }
+#pragma unroll
+    for (int jj = 0; jj < 4; ++jj)
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        const int c = n0 + acc_col<B_KC>(wn, jj, 2 * t + e);
+        if ((live >> (jj * 2 + e)) & 1u) C[r + (int64_t)c * p.ldc] = fma(beta, o[jj][e], alpha * acc[i][jj][e]);
       }
   }
 }

@@ -11,7 +11,8 @@ enum { CAP_WS_GEMM_SPLITK = 0, CAP_WS_TRI = 1, CAP_WS_PANEL = 2, CAP_WS_FACTOR =
        CAP_WS_VALID = 17,                                                                      // validators: accumulators, block partials, product chunk
        CAP_WS_GEMM_SPLITK2 = 18,                                                               // split-K partials of launches on the panel stream (bank 1)
        CAP_WS_POTRF1D = 19,                                                                    // look-ahead Cholesky: inverse block, row panels (double-buffered)
-       CAP_WS_SLOTS = 20 };
+       CAP_WS_GEMM_SPLITK3 = 20,                                                               // split-K partials of launches on the row stream (bank 2)
+       CAP_WS_SLOTS = 21 };
 
 struct cap_ws_slot { void* ptr = nullptr; size_t bytes = 0; };
 
@@ -46,15 +47,15 @@ struct cap_handle_s {
   int lookahead_pipeline = -1;        // -1 = the asynchronous schedule (potrf_1d.cuh), 0 / 1 = round-1 two-stream / pipelined NCCL orders
   // asynchronous look-ahead Cholesky (potrf_1d.cuh): ring of events, exchange / signal streams, peer-mapped landing buffers
   enum { RING = 4 };
-  cudaStream_t xchg_stream = nullptr, sig_stream = nullptr;
-  cudaEvent_t ev_leaf[RING] = {}, ev_csolve[RING] = {}, ev_solve[RING] = {}, ev_xchg[RING] = {}, ev_xpush[RING] = {}, ev_r1[RING] = {}, ev_r2a[RING] = {}, ev_r2[RING] = {};
+  cudaStream_t xchg_stream = nullptr, sig_stream = nullptr, row_stream = nullptr;
+  cudaEvent_t ev_leaf[RING] = {}, ev_csolve[RING] = {}, ev_solve[RING] = {}, ev_xchg[RING] = {}, ev_xpush[RING] = {}, ev_rowready[RING] = {}, ev_r1[RING] = {}, ev_r2a[RING] = {}, ev_r2[RING] = {};
   cap_peer_s* peer1d = nullptr;       // landing buffers of the panel exchange (owned)
   int peer_exchange = -1;             // -1 = peer copy engines when CUDA IPC works, else NCCL; 0 = NCCL orders of round 1; 1 = required
   void* fn_wait32 = nullptr;          // cuStreamWaitValue32 / cuStreamWriteValue32 (driver entry points)
   void* fn_write32 = nullptr;
   uint32_t* sig_scratch = nullptr;    // one word per signalling stream: the value a 4-byte peer copy carries
   struct cap_comm_s* peer_failed_comm = nullptr;   // CUDA IPC mapping failed on this communicator: do not retry every call
-  int lookahead_grid_mult = 0;        // tile-engine grid multiplier of the trailing update beside a chain (0 = keep the persistent grid)
+  int lookahead_grid_mult = 64;       // tile-engine grid multiplier of the trailing update beside a chain (0 = keep the persistent grid)
   int lookahead_stair = 1;            // trailing update of the asynchronous schedule as ONE staircase launch (0 = a gemm + a syrk per run of blocks)
   int grid_mult = 1;                  // tile engine: CTAs per SM worth of grid (1 = persistent, one CTA per SM)
   int ws_bank = 0;                    // which split-K workspace slot gemm launches use (1 while launching on the panel stream)

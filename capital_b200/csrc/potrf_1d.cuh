@@ -104,16 +104,27 @@ struct Timeline1D {
   void report(cudaStream_t main_stream, int rank, const Layout1D& L) {
     if (!on || stamps.empty()) return;
     cudaStreamSynchronize(main_stream);
-    fprintf(stderr, "[capital_b200 timeline] rank %d  potrf_1d N=%lld nb=%d P=%d  (ms since the first stamp; begin..end per phase)\n", rank, (long long)L.N, L.nb, L.P);
+    cudaDeviceSynchronize();
+    std::string out;
+    char line[256];
+    snprintf(line, sizeof line, "[capital_b200 timeline] rank %d  potrf_1d N=%lld nb=%d P=%d  (ms since the first stamp; begin..end per phase)\n", rank, (long long)L.N, L.nb, L.P);
+    out += line;
     int cur = -1;
     for (size_t i = 0; i + 1 < stamps.size(); i += 2) {       // stamps come in begin/end pairs
       float t0 = 0, t1 = 0;
       cudaEventElapsedTime(&t0, stamps[0].ev, stamps[i].ev);
       cudaEventElapsedTime(&t1, stamps[0].ev, stamps[i + 1].ev);
-      if (stamps[i].panel != cur) { cur = stamps[i].panel; fprintf(stderr, "%s  panel %3d (owner %d):", i ? "\n" : "", cur, L.owner(cur)); }
-      fprintf(stderr, "  %s %.3f..%.3f", stamps[i].what, t0, t1);
+      if (stamps[i].panel != cur) { cur = stamps[i].panel; snprintf(line, sizeof line, "%s  panel %3d (owner %d):", i ? "\n" : "", cur, L.owner(cur)); out += line; }
+      snprintf(line, sizeof line, "  %s %.3f..%.3f", stamps[i].what, t0, t1);
+      out += line;
     }
-    fprintf(stderr, "\n");
+    out += "\n";
+    // CAPITAL_B200_PROFILE_FILE=<prefix>: one file per rank (ranks print at the same time; a shared stderr interleaves them)
+    const char* prefix = getenv("CAPITAL_B200_PROFILE_FILE");
+    FILE* f = nullptr;
+    if (prefix) { snprintf(line, sizeof line, "%s.rank%d.txt", prefix, rank); f = fopen(line, "w"); }
+    fwrite(out.data(), 1, out.size(), f ? f : stderr);
+    if (f) fclose(f);
     for (auto& st : stamps) cudaEventDestroy(st.ev);
     stamps.clear();
   }
@@ -356,7 +367,7 @@ struct Async1D {
   double *X[RING], *S[RING], *R[RING], *Wleaf;
   size_t off_X[RING], off_R[RING], off_flag_x, off_flag_r, off_ack;   // byte offsets inside the symmetric buffer
   uint32_t base;
-  cudaStream_t sm, sp, sc, sx;
+  cudaStream_t sm, sr, sp, sc, sx;     // bulk trailing update (the caller's stream), row work, chain, exchange, signals
 
   double* blockptr(int row_block, int local_block) const { return A + (int64_t)row_block * L.nb + (int64_t)local_block * L.nb * lda; }
   uint32_t seq(int j) const { return base + (uint32_t)j + 1u; }
@@ -446,16 +457,16 @@ struct Async1D {
   int solve_rest(int j) {                            // row j right of block j, minus the block the chain solves; then ship it
     const int b = j % RING, nb = L.nb;
     if (j >= L.nblk - 1) return CAP_OK;
-    CAP_TRY(get_x(sm, j));
-    if (j >= RING && peer) CUDA_TRY(cudaStreamWaitEvent(sm, h->ev_xchg[b], 0));
+    CAP_TRY(get_x(sr, j));
+    if (j >= RING && peer) CUDA_TRY(cudaStreamWaitEvent(sr, h->ev_xchg[b], 0));
     int r_first = r0_of(j);
     const bool chain_block = (me == L.owner(j + 1));
     if (chain_block) ++r_first;
-    tl.mark(sm, j, "solve");
+    tl.mark(sr, j, "solve");
     CAP_TRY(solve_cols(j, r_first, cols_from(r_first)));
     CAP_TRY(self_copy(j, r_first, L.nloc(me)));
-    tl.mark(sm, j, "solve");
-    CUDA_TRY(cudaEventRecord(h->ev_solve[b], sm));
+    tl.mark(sr, j, "solve");
+    CUDA_TRY(cudaEventRecord(h->ev_solve[b], sr));
     if (!peer) return CAP_OK;
     // exchange(j) on C
     CUDA_TRY(cudaStreamWaitEvent(sc, h->ev_solve[b], 0));
@@ -481,12 +492,12 @@ struct Async1D {
   int row_data_ready(int j) {                        // every block of the ordered row panel j is in R[b]
     const int b = j % RING;
     if (me == L.owner(j + 1)) {
-      CUDA_TRY(cudaStreamWaitEvent(sm, h->ev_csolve[b], 0));
+      CUDA_TRY(cudaStreamWaitEvent(sr, h->ev_csolve[b], 0));
       CAP_TRY(self_copy(j, r0_of(j), r0_of(j) + 1));
     }
     if (!peer) return CAP_OK;
     for (int p = 0; p < L.P; ++p)
-      if (p != me && L.cols_right(p, j) > 0) CAP_TRY(wait_flag(sm, off_flag_r + ((size_t)p * RING + b) * 4, seq(j)));
+      if (p != me && L.cols_right(p, j) > 0) CAP_TRY(wait_flag(sr, off_flag_r + ((size_t)p * RING + b) * 4, seq(j)));
     return CAP_OK;
   }
   int update_row(int j) {                            // U1rest(j): block row j+1, columns right of block j+1
@@ -531,6 +542,12 @@ struct Async1D {
     return CAP_OK;
   }
 
+  // Host order = the order in which every event is recorded before anything waits on it.
+  //   R (row stream, above the caller's priority): [row j here] [bulk(j-1) done] U1rest(j) -> U2a(j) -> solve rest of row j+1 -> (C) ship it
+  //   M (the caller's stream):                      [row j here] U2b(j), the bulk of the trailing update, as ONE staircase launch
+  // U1rest(j) touches block row j+1 only and U2b(j) rows >= j+2, so they run side by side: the row work of a panel (two
+  // partial waves of the tile engine, a triangular solve, the copy-engine exchange) hides inside the bulk of the same panel
+  // instead of delaying it.  bulk(j) -> U1rest(j+1) is ordered by an event (both update block row j+2).
   int run() {
     const int nblk = L.nblk;
     {
@@ -538,27 +555,34 @@ struct Async1D {
       if (me == L.owner(0)) CAP_TRY(leaf_and_push(0));
     }
     if (nblk > 1) CAP_TRY(chain_front(1));            // before solve_rest(0): its events are waited on by the exchange of panel 0
-    { StreamScope scope(h, sm, 0); CAP_TRY(solve_rest(0)); }
+    { StreamScope scope(h, sr, 2); CAP_TRY(solve_rest(0)); }
     // SMs left to the chain: only while a chain runs on THIS rank beside the work being launched
     auto reserve_for = [&](int k) { return (k < nblk && (L.P == 1 || me == L.owner(k)) && h->lookahead_reserve_sms > 0) ? h->num_sms - h->lookahead_reserve_sms : 0; };
     for (int j = 0; j + 1 < nblk; ++j) {
       const int b = j % RING;
       {
-        StreamScope scope(h, sm, 0);
+        StreamScope scope(h, sr, 2);
         SmCapScope cap(h, reserve_for(j + 1));         // leaf(j+1) may still be running here
         CAP_TRY(row_data_ready(j));
-        tl.mark(sm, j, "U1");
+        CUDA_TRY(cudaEventRecord(h->ev_rowready[b], sr));
+        if (j > 0) CUDA_TRY(cudaStreamWaitEvent(sr, h->ev_r2[(j - 1) % RING], 0));     // bulk(j-1) also updated block row j+1
+        tl.mark(sr, j, "U1");
         CAP_TRY(update_row(j));
-        CUDA_TRY(cudaEventRecord(h->ev_r1[b], sm));
+        CUDA_TRY(cudaEventRecord(h->ev_r1[b], sr));
         CAP_TRY(update_diag2(j));
-        tl.mark(sm, j, "U1");
-        CUDA_TRY(cudaEventRecord(h->ev_r2a[b], sm));
+        tl.mark(sr, j, "U1");
+        CUDA_TRY(cudaEventRecord(h->ev_r2a[b], sr));
       }
       if (j + 2 < nblk) CAP_TRY(chain_front(j + 2));
       {
-        StreamScope scope(h, sm, 0);
+        StreamScope scope(h, sr, 2);
         SmCapScope cap(h, reserve_for(j + 2));         // the chain of panel j+2 runs beside the rest of this iteration
         CAP_TRY(solve_rest(j + 1));
+      }
+      {
+        StreamScope scope(h, sm, 0);
+        SmCapScope cap(h, reserve_for(j + 2));
+        CUDA_TRY(cudaStreamWaitEvent(sm, h->ev_rowready[b], 0));
         if (j + 2 < nblk) {
           GridMultScope gm(h, h->lookahead_grid_mult);
           tl.mark(sm, j, "U2");
@@ -567,13 +591,16 @@ struct Async1D {
         }
         CUDA_TRY(cudaEventRecord(h->ev_r2[b], sm));
       }
-      if (peer) {                                     // panel j's landing buffers here are free again: tell every peer
+      if (peer) {                                     // panel j's landing buffers here are free again (bulk AND row work read them): tell every peer
         CUDA_TRY(cudaStreamWaitEvent(sx, h->ev_r2[b], 0));
+        CUDA_TRY(cudaStreamWaitEvent(sx, h->ev_r2a[b], 0));
         for (int i = 1; i < L.P; ++i) CAP_TRY(signal(sx, 1, (me + i) % L.P, off_ack + (size_t)me * 4, seq(j)));
       }
     }
-    // join: the last leaf (P) is ordered before whatever follows on the caller's stream; then the final acknowledgement
+    // join: the last leaf (P) and the last row work (R) are ordered before whatever follows on the caller's stream; then the final acknowledgement
     CUDA_TRY(cudaEventRecord(h->ev_panel[0], sp));
+    CUDA_TRY(cudaStreamWaitEvent(sm, h->ev_panel[0], 0));
+    CUDA_TRY(cudaEventRecord(h->ev_panel[0], sr));
     CUDA_TRY(cudaStreamWaitEvent(sm, h->ev_panel[0], 0));
     if (peer) {
       CUDA_TRY(cudaEventRecord(h->ev_panel[1], sm));
@@ -591,8 +618,9 @@ static int async_streams(cap_handle_t h) {
   CUDA_TRY(cudaDeviceGetStreamPriorityRange(&lo, &hi));
   CUDA_TRY(cudaStreamCreateWithPriority(&h->xchg_stream, cudaStreamNonBlocking, hi));
   CUDA_TRY(cudaStreamCreateWithPriority(&h->sig_stream, cudaStreamNonBlocking, hi));
+  CUDA_TRY(cudaStreamCreateWithPriority(&h->row_stream, cudaStreamNonBlocking, hi < lo - 1 ? hi + 1 : hi));   // between the chain and the caller's stream
   for (int i = 0; i < cap_handle_s::RING; ++i)
-    for (cudaEvent_t* e : {&h->ev_leaf[i], &h->ev_csolve[i], &h->ev_solve[i], &h->ev_xchg[i], &h->ev_xpush[i], &h->ev_r1[i], &h->ev_r2a[i], &h->ev_r2[i]})
+    for (cudaEvent_t* e : {&h->ev_leaf[i], &h->ev_csolve[i], &h->ev_solve[i], &h->ev_xchg[i], &h->ev_xpush[i], &h->ev_rowready[i], &h->ev_r1[i], &h->ev_r2a[i], &h->ev_r2[i]})
       CUDA_TRY(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
   CUDA_TRY(cudaMalloc((void**)&h->sig_scratch, 64));
   for (const char* name : {"cuStreamWaitValue32", "cuStreamWriteValue32"}) {
@@ -668,10 +696,10 @@ int cap_potrf_1d(cap_handle_t h, cap_comm_t comm, int64_t N, int nb, double* A_l
         for (int b = 0; b < RING; ++b) { a.off_R[b] = off; a.R[b] = (double*)(peer->ptr[me] + off); off += rs * sizeof(double); }
         a.base = peer->seq;
       }
-      a.sm = h->stream; a.sp = h->panel_stream; a.sc = h->xchg_stream; a.sx = h->sig_stream;
+      a.sm = h->stream; a.sr = h->row_stream; a.sp = h->panel_stream; a.sc = h->xchg_stream; a.sx = h->sig_stream;
       // the side streams start behind everything already enqueued on the caller's stream
       CUDA_TRY(cudaEventRecord(h->ev_u1, a.sm));
-      for (cudaStream_t s : {a.sp, a.sc, a.sx}) CUDA_TRY(cudaStreamWaitEvent(s, h->ev_u1, 0));
+      for (cudaStream_t s : {a.sr, a.sp, a.sc, a.sx}) CUDA_TRY(cudaStreamWaitEvent(s, h->ev_u1, 0));
       const char* prof = getenv("CAPITAL_B200_PROFILE");
       a.tl.on = prof && (atoi(prof) >= 2 || (atoi(prof) == 1 && me == 0));
       const int rc = a.run();

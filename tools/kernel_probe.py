@@ -38,6 +38,7 @@ def main():
     ap.add_argument("--n", type=int, default=1024)
     ap.add_argument("--N", type=int, default=8192)
     ap.add_argument("--profile", action="store_true")
+    ap.add_argument("--K", type=int, nargs="+", default=[1024], help="contraction lengths of the `update` case")
     args = ap.parse_args()
     global PROFILE
     PROFILE = args.profile
@@ -50,6 +51,14 @@ def main():
             best, avg = timeit(lambda: E._gemm(A, B, Cm, N, N, N, ta, tb), args.reps)
             print("%s N=%d: best %.3f ms avg %.3f ms  %.2f TFLOP/s" % (case, N, best, avg, 2 * N ** 3 / best * 1e-9), flush=True)
             del A, B, Cm
+        elif case == "update":
+            # the shape of the Cholesky trailing update: C(M x Nc) -= A^T B, A: K x M, B: K x Nc, both k-contiguous, beta = 1
+            M, Nc = 2 * N, N // 2
+            for K in args.K:
+                A = colmajor(K, M); B = colmajor(K, Nc); Cm = colmajor(M, Nc); A.uniform_(); B.uniform_(); Cm.zero_()
+                best, avg = timeit(lambda: E._gemm(A, B, Cm, M, Nc, K, "T", "N", -1.0, 1.0), args.reps)
+                print("update M=%d N=%d K=%d: best %.3f ms avg %.3f ms  %.2f TFLOP/s" % (M, Nc, K, best, avg, 2.0 * M * Nc * K / best * 1e-9), flush=True)
+                del A, B, Cm
         elif case in ("apply", "gram", "cqr2", "apply_inplace"):
             A = colmajor(m, n); E.fill_random(A, 1); Q = colmajor(m, n); R = colmajor(n, n); G = colmajor(n, n); X = colmajor(n, n)
             E.cqr_gram(A, G); E.cholinv(G, X, n, True)
