@@ -32,6 +32,42 @@ def test_grid_algorithms(world, n):
     _run_grid_check(world, n, 29540 + world)
 
 
+def test_reference_engine_headers_bound_to_device(tmp_path):
+    """integration/_build/engine_check = the reference's UNMODIFIED src/blas/{engine.h,interface.h} and
+    src/lapack/{engine.h,interface.h} compiled (in the build container, integration/Makefile) with
+    integration/{blas,lapack}/interface.hpp in place of the CBLAS / LAPACKE specialisations.  Operands and expected
+    results: tests/golden/engines.npz, the outputs of the reference's own engines on the CPU."""
+    exe = os.path.join(ROOT, "integration", "_build", "engine_check")
+    if not os.path.exists(exe):
+        pytest.skip("integration/_build/engine_check not built (make -C integration, needs /root/reference)")
+    z = np.load(os.path.join(ROOT, "tests", "golden", "engines.npz"))
+    put = lambda name, a: np.asfortranarray(a).T.copy().tofile(str(tmp_path / name))      # column-major raw doubles
+    lines, expect = [], {}
+    for tag in ("NN", "TN", "NT", "TT"):
+        A, B, C0, C = (z["gemm_%s_%s" % (tag, k)] for k in ("A", "B", "C0", "C"))
+        m, n = C.shape; k = A.shape[0] if tag[0] == "T" else A.shape[1]
+        put("g%sA" % tag, A); put("g%sB" % tag, B); put("g%sC" % tag, C0)
+        lines.append("gemm %s %s %d %d %d 1.25 -0.5 g%sA g%sB g%sC g%sO" % (tag[0], tag[1], m, n, k, tag, tag, tag, tag))
+        expect["g%sO" % tag] = (C, None)
+    A, C0, C = z["syrk_A"], z["syrk_C0"], z["syrk_C"]
+    put("sA", A); put("sC", C0)
+    lines.append("syrk U T %d %d 1.0 0.0 sA sC sO" % (C.shape[0], A.shape[0])); expect["sO"] = (C, "U")
+    for tag in ("RUN", "LUT", "LUN", "RLT"):
+        T, B0, B = z["trmm_%s_T" % tag], z["trmm_%s_B0" % tag], z["trmm_%s_B" % tag]
+        put("t%sT" % tag, T); put("t%sB" % tag, B0)
+        lines.append("trmm %s %s %s N %d %d -1.0 t%sT t%sB t%sO" % (tag[0], tag[1], tag[2], B.shape[0], B.shape[1], tag, tag, tag)); expect["t%sO" % tag] = (B, None)
+    put("pA", z["potrf_A"]); lines.append("potrf U %d pA pO" % z["potrf_A"].shape[0]); expect["pO"] = (z["potrf_R"], "U")
+    put("xT", z["trtri_T"]); lines.append("trtri U N %d xT xO" % z["trtri_T"].shape[0]); expect["xO"] = (z["trtri_X"], "U")
+    (tmp_path / "cases.txt").write_text("\n".join(lines) + "\n")
+    out = subprocess.run([exe, str(tmp_path)], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0 and "%d cases" % len(lines) in out.stdout, out.stdout[-2000:] + out.stderr[-2000:]
+    for name, (want, tri) in expect.items():
+        got = np.fromfile(str(tmp_path / name)).reshape(want.shape[1], want.shape[0]).T
+        if tri == "U":
+            got, want = np.triu(got), np.triu(want)
+        assert relerr(got, want) <= TOL_FACTOR, name
+
+
 def test_cpp_host_drivers():
     """The reference's bench command lines (bench/qr/cacqr.cpp:14-25, bench/cholesky/cholinv.cpp:15-22,
     bench/matmult/summa_gemm.cpp:19-25) run against the C++ host mirror."""
