@@ -30,6 +30,7 @@ _SIGS = {
     "cap_copy2d": [_ptr, _ptr, _i64, _ptr, _i64, _i64, _i64, _int],
     "cap_pack_upper": [_ptr, _ptr, _ptr, _i64, _int], "cap_unpack_upper": [_ptr, _ptr, _i64, _ptr, _int, _int],
     "cap_axpby": [_ptr, _ptr, _ptr, _i64, _dbl, _dbl],
+    "cap_axpby2d": [_ptr, _ptr, _i64, _ptr, _i64, _i64, _i64, _dbl, _dbl], "cap_fill_diagonal": [_ptr, _ptr, _i64, _i64, _dbl],
     "cap_fill_random": [_ptr, _ptr, _i64, _i64, _i64, C.c_longlong],
     "cap_fill_symmetric": [_ptr, _ptr, _i64, _i64, _i64, _i64, _i64, _i64, _i64, _i64, _int],
     "cap_comm_unique_id": [C.c_char_p], "cap_comm_init_rank": [C.POINTER(_ptr), C.c_char_p, _int, _int],
@@ -38,7 +39,7 @@ _SIGS = {
     "cap_allreduce_sum": [_ptr, _ptr, _ptr, _i64], "cap_reduce_sum": [_ptr, _ptr, _ptr, _i64, _int],
     "cap_bcast": [_ptr, _ptr, _ptr, _i64, _int], "cap_allgather": [_ptr, _ptr, _ptr, _ptr, _i64],
     "cap_sendrecv": [_ptr, _ptr, _ptr, _ptr, _i64, _int],
-    "cap_grid_create": [_ptr, _int, C.POINTER(_ptr)], "cap_grid_destroy": [_ptr],
+    "cap_grid_create": [_ptr, _int, C.POINTER(_ptr)], "cap_grid_create2": [_ptr, _int, _int, _int, C.POINTER(_ptr)], "cap_grid_set_chunks": [_ptr, _int], "cap_grid_destroy": [_ptr],
     "cap_grid_info": [_ptr] + [C.POINTER(_int)] * 5, "cap_grid_transpose": [_ptr, _ptr, _ptr, _ptr, _i64],
     "cap_summa_gemm": [_ptr, _ptr, _chr, _chr, _i64, _i64, _i64, _dbl, _ptr, _i64, _ptr, _i64, _dbl, _ptr, _i64],
     "cap_summa_trmm": [_ptr, _ptr, _chr, _chr, _chr, _chr, _i64, _i64, _dbl, _ptr, _i64, _ptr, _i64],

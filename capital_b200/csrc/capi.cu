@@ -98,6 +98,10 @@ int cap_destroy(cap_handle_t h) {
   cudaStreamSynchronize(h->stream);
   for (auto& w : h->ws) if (w.ptr) cudaFree(w.ptr);
   if (h->info_dev) cudaFree(h->info_dev);
+  if (h->summa_stream) {
+    cudaStreamDestroy(h->summa_stream);
+    for (cudaEvent_t e : {h->ev_sready[0], h->ev_sready[1], h->ev_sfree[0], h->ev_sfree[1], h->ev_shalf, h->ev_sred[0], h->ev_sred[1], h->ev_sstart}) cudaEventDestroy(e);
+  }
   if (h->ev_a) cudaEventDestroy(h->ev_a);
   if (h->ev_b) cudaEventDestroy(h->ev_b);
   if (h->panel_stream) {
@@ -389,9 +393,16 @@ int cap_dsyrk(cap_handle_t h, char uplo, char trans, int64_t n, int64_t k, doubl
   return gemm_launch(h, p, tr, !tr, -1);
 }
 
-__global__ void set_unit_diag_kernel(double* T, int64_t ld, int n) {
+__global__ void set_unit_diag_kernel(double* T, int64_t ld, int n, double v = 1.0) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) T[i + (int64_t)i * ld] = 1.0;
+  if (i < n) T[i + (int64_t)i * ld] = v;
+}
+int cap_fill_diagonal(cap_handle_t h, double* dst, int64_t ld, int64_t n, double value) {
+  if (n <= 0) return CAP_OK;
+  if (n > INT32_MAX) return cap_fail(CAP_ERR_ARG, "cap_fill_diagonal", "bad dimension");
+  set_unit_diag_kernel<<<(unsigned)((n + 255) / 256), 256, 0, h->stream>>>(dst, ld, (int)n, value);
+  LAUNCH_CHECK(h);
+  return CAP_OK;
 }
 
 // C = alpha*op(T)*B (left) or alpha*B*op(T) (right).  t_clean: the other triangle of T is already zero.
@@ -900,5 +911,15 @@ int cap_validate_cacqr_1d(cap_handle_t h, cap_comm_t comm, int64_t m_loc, int64_
   return cap_residual_finish(h, comm, resid);
 }
 
+struct StreamScope {   // the helpers launch on h->stream: switch it (and the split-K workspace bank) for a scope
+  cap_handle_t h; cudaStream_t saved; int saved_bank;
+  StreamScope(cap_handle_t h_, cudaStream_t s, int bank) : h(h_), saved(h_->stream), saved_bank(h_->ws_bank) { h->stream = s; h->ws_bank = bank; }
+  ~StreamScope() { h->stream = saved; h->ws_bank = saved_bank; }
+};
+
 #include "grid_algs.cuh"
 #include "potrf_1d.cuh"
+
+int cap_axpby2d(cap_handle_t h, double* y, int64_t ldy, const double* x, int64_t ldx, int64_t m, int64_t n, double alpha, double beta) {
+  return axpby2d(h, y, ldy, x, ldx, m, n, alpha, beta, CTRI_FULL);
+}

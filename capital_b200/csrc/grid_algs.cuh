@@ -18,11 +18,16 @@
 struct cap_grid_s {
   cap_comm_t world = nullptr, row = nullptr, column = nullptr, depth = nullptr, slice = nullptr;
   int c = 1, d = 1, x = 0, y = 0, z = 0, rank = 0, size = 1;
+  int num_chunks = 0;          // pieces per panel of the pipelined SUMMA (0 = chosen from the contraction length); topo's num_chunks
+  int layout = 0;              // 0: z fastest, then x, then y; 1: y fastest, then x, then z (topology.h:80-110)
+  int rank_of(int xx, int yy, int zz) const { return layout == 0 ? zz + c * (xx + d * yy) : yy + d * (xx + d * zz); }
 };
 
-int cap_grid_create(cap_comm_t world, int c, cap_grid_t* out) {
+int cap_grid_create2(cap_comm_t world, int c, int layout, int num_chunks, cap_grid_t* out) {
+  if (layout != 0 && layout != 1) return cap_fail(CAP_ERR_UNSUPPORTED, "cap_grid_create", "layout must be 0 or 1 (topology.h:80-110)");
+  if (num_chunks < 0) return cap_fail(CAP_ERR_ARG, "cap_grid_create", "num_chunks must be >= 0");
   cap_grid_s* g = new cap_grid_s();
-  g->world = world; g->c = c;
+  g->world = world; g->c = c; g->layout = layout; g->num_chunks = num_chunks;
   if (world) { cap_comm_rank(world, &g->rank); cap_comm_size(world, &g->size); }
   int d = 1;
   while ((int64_t)c * (d + 1) * (d + 1) <= g->size) ++d;
@@ -31,15 +36,24 @@ int cap_grid_create(cap_comm_t world, int c, cap_grid_t* out) {
     return cap_fail(CAP_ERR_ARG, "cap_grid_create", "need size == c*d*d with d % c == 0 (or d == 1)");
   }
   g->d = d;
-  // layout 0 of topo::square (topology.h:80-95): z fastest, then x, then y
-  g->z = g->rank % c; g->y = g->rank / (d * c); g->x = (g->rank % (d * c)) / c;
+  if (layout == 0) {   // topology.h:80-95: z fastest, then x, then y
+    g->z = g->rank % c; g->y = g->rank / (d * c); g->x = (g->rank % (d * c)) / c;
+  } else {             // topology.h:96-110: y fastest, then x, then z
+    g->y = g->rank % d; g->x = (g->rank % (d * d)) / d; g->z = g->rank / (d * d);
+  }
   if (g->size > 1) {
-    CAP_TRY(cap_comm_split(world, g->rank / c, g->rank, &g->depth));        // same (x, y): rank in comm = z
-    CAP_TRY(cap_comm_split(world, g->z, g->rank, &g->slice));               // same z: rank in comm = x + d*y
+    CAP_TRY(cap_comm_split(world, g->x + d * g->y, g->z, &g->depth));       // same (x, y): rank in comm = z
+    CAP_TRY(cap_comm_split(world, g->z, g->x + d * g->y, &g->slice));       // same z: rank in comm = x + d*y
     CAP_TRY(cap_comm_split(g->slice, g->y, g->x, &g->row));                 // same (y, z): rank in comm = x
     CAP_TRY(cap_comm_split(g->slice, g->x, g->y, &g->column));              // same (x, z): rank in comm = y
   }
   *out = g;
+  return CAP_OK;
+}
+int cap_grid_create(cap_comm_t world, int c, cap_grid_t* out) { return cap_grid_create2(world, c, 0, 0, out); }
+int cap_grid_set_chunks(cap_grid_t g, int num_chunks) {
+  if (num_chunks < 0) return cap_fail(CAP_ERR_ARG, "cap_grid_set_chunks", "num_chunks must be >= 0");
+  g->num_chunks = num_chunks;
   return CAP_OK;
 }
 int cap_grid_destroy(cap_grid_t g) {
@@ -55,7 +69,7 @@ int cap_grid_info(cap_grid_t g, int* c, int* d, int* x, int* y, int* z) {
 
 // util::transpose (util.hpp:233-247): exchange the local block with the process at (y, x) of the same layer.
 int cap_grid_transpose(cap_handle_t h, cap_grid_t g, const double* src, double* dst, int64_t count) {
-  const int partner = g->z + g->c * (g->y + g->d * g->x);
+  const int partner = g->rank_of(g->y, g->x, g->z);
   return cap_sendrecv(h, g->size > 1 ? g->world : nullptr, src, dst, count, partner == g->rank ? g->rank : partner);
 }
 
@@ -126,6 +140,134 @@ static int summa_local(cap_handle_t h, const SummaOp& op, int64_t m, int64_t n, 
   return trmm_impl(h, 'R', op.uplo, op.trans, op.diag, m, n, op.alpha, R, ldr, L, ldl, target, ldt, op.t_clean, false, beta);
 }
 
+// d > 1: the panel loop of summa::distribute / collect with communication and computation overlapped -- the job of the
+// reference's num_chunks pipeline (summa.hpp:196-215 chunked MPI_Ibcast, :238-249 chunked MPI_Iallreduce).  Both operands
+// of a panel are cut along the CONTRACTION index into num_chunks pieces; piece q+1 travels (row broadcast of the left
+// piece, column broadcast of the right piece, on the handle's communication stream) while piece q is multiplied on the
+// compute stream.  With depth c > 1 the columns of C are done in two halves so that the depth all-reduce of the first
+// half runs beside the products of the second.  The root packs each piece into the landing buffer (one device copy) and
+// broadcasts in place, so pieces are dense whatever the leading dimension or orientation of the operand.
+// Triangular operands: a piece only touches the rows (left) / columns (right) of C on its side of the diagonal, so the
+// product is restricted to that range -- the structural zeros of a piece cost at most 1 / (2 num_chunks) of the flops.
+static int summa_streams(cap_handle_t h) {
+  if (h->summa_stream) return CAP_OK;
+  int lo = 0, hi = 0;
+  CUDA_TRY(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+  CUDA_TRY(cudaStreamCreateWithPriority(&h->summa_stream, cudaStreamNonBlocking, hi));
+  for (cudaEvent_t* e : {&h->ev_sready[0], &h->ev_sready[1], &h->ev_sfree[0], &h->ev_sfree[1], &h->ev_shalf, &h->ev_sred[0], &h->ev_sred[1], &h->ev_sstart})
+    CUDA_TRY(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+  return CAP_OK;
+}
+
+static int summa_pipelined(cap_handle_t h, cap_grid_t g, const SummaOp& op, int64_t m, int64_t n, int64_t k,
+                           const double* L, int64_t ldl, int64_t lr, int64_t lc, const double* R, int64_t ldr, int64_t rr, int64_t rc,
+                           double beta, double* C, int64_t ldc, double* S, int64_t lds, bool direct) {
+  const int c = g->c, d = g->d, steps = d / c;
+  CAP_TRY(summa_streams(h));
+  cudaStream_t ms = h->stream, cs = h->summa_stream;
+  // how each stored operand is cut along the contraction index: by columns (dense, ld = rows) or by rows (packed, ld = piece)
+  bool l_by_col, r_by_col;
+  if (op.kind == SUMMA_GEMM) { l_by_col = !is_t(op.ta); r_by_col = is_t(op.tb); }
+  else if (op.kind == SUMMA_TRMM_L) { l_by_col = !is_t(op.trans); r_by_col = false; }
+  else { l_by_col = true; r_by_col = is_t(op.trans); }
+  const bool tri = op.kind != SUMMA_GEMM;
+  if (tri && (!op.t_clean || is_u(op.diag))) return cap_fail(CAP_ERR_UNSUPPORTED, "summa trmm", "pipelined path needs a clean non-unit triangular operand");
+  int nq = g->num_chunks > 0 ? g->num_chunks : (int)std::max<int64_t>(1, std::min<int64_t>(8, k / 2048));
+  nq = (int)std::min<int64_t>(nq, std::max<int64_t>(1, k / 128));
+  const int64_t kc_max = ((k + nq - 1) / nq + 127) / 128 * 128;
+  nq = (int)((k + kc_max - 1) / kc_max);
+  const int nh = (c > 1 && n >= 256) ? 2 : 1;
+  const int64_t nh0 = nh == 2 ? ((n / 2 + 127) / 128) * 128 : n;       // columns of the first half
+  double *Lbuf, *Rbuf;
+  CAP_TRY(cap_workspace(h, CAP_WS_SUMMA_A, (size_t)lr * lc * sizeof(double), &Lbuf));
+  const int64_t r_other = r_by_col ? rr : rc;                              // extent of R across the contraction index
+  CAP_TRY(cap_workspace(h, CAP_WS_SUMMA_B, (size_t)2 * kc_max * r_other * sizeof(double), &Rbuf));
+  const bool zero_first = tri || !direct;                                  // restricted products never write the whole of S
+  if (zero_first && !direct) CAP_TRY(memset2d(h, S, lds, m, n));
+  // the communication stream starts behind everything enqueued so far (the landing buffers may still be read)
+  CUDA_TRY(cudaEventRecord(h->ev_sstart, ms));
+  CUDA_TRY(cudaStreamWaitEvent(cs, h->ev_sstart, 0));
+  int seq = 0;                                                             // running piece number -> R buffer seq & 1
+  bool used[2] = {false, false};
+  for (int hf = 0; hf < nh; ++hf) {
+    const int64_t n0 = hf == 0 ? 0 : nh0, n1 = (hf == 0 && nh == 2) ? nh0 : n;
+    for (int s = 0; s < steps; ++s) {
+      const int kp = g->z + s * c;
+      for (int q = 0; q < nq; ++q, ++seq) {
+        const int64_t k0 = (int64_t)q * kc_max, k1 = std::min<int64_t>(k, k0 + kc_max), kc = k1 - k0;
+        const int bufi = seq & 1;
+        double* Lq = Lbuf + (l_by_col ? k0 * lr : k0 * lc);               // piece q of the left operand: lr x kc (ld lr) or kc x lc (ld kc)
+        const int64_t ldlq = l_by_col ? lr : kc;
+        double* Rq = Rbuf + (size_t)bufi * kc_max * r_other;              // piece of the right operand restricted to the half's columns
+        const int64_t rcols = n1 - n0;
+        const int64_t ldrq = r_by_col ? rcols : kc;                       // by column: (n1-n0) x kc stored; by row: kc x (n1-n0)
+        {
+          StreamScope scope(h, cs, 0);
+          if (used[bufi]) CUDA_TRY(cudaStreamWaitEvent(cs, h->ev_sfree[bufi], 0));
+          if (hf == 0 || steps > 1) {      // the left piece travels once per panel; with several panels its landing buffer is reused
+            if (g->x == kp) {
+              if (l_by_col) CAP_TRY(copy2d(h, Lq, lr, L + k0 * ldl, ldl, lr, kc, 0));
+              else CAP_TRY(copy2d(h, Lq, kc, L + k0, ldl, kc, lc, 0));
+            }
+            CAP_TRY(cap_bcast(h, g->row, Lq, (l_by_col ? lr : lc) * kc, kp));
+          }
+          if (g->y == kp) {
+            if (r_by_col) CAP_TRY(copy2d(h, Rq, rcols, R + n0 + k0 * ldr, ldr, rcols, kc, 0));
+            else CAP_TRY(copy2d(h, Rq, kc, R + k0 + n0 * ldr, ldr, kc, rcols, 0));
+          }
+          CAP_TRY(cap_bcast(h, g->column, Rq, rcols * kc, kp));
+          CUDA_TRY(cudaEventRecord(h->ev_sready[bufi], cs));
+        }
+        CUDA_TRY(cudaStreamWaitEvent(ms, h->ev_sready[bufi], 0));
+        // ---- the product of this piece on the compute stream: S[mlo:mhi, n0+nlo : n0+nhi] += alpha * op(Lq) * op(Rq)
+        int64_t mlo = 0, mhi = m, nlo = n0, nhi = n1;
+        if (op.kind == SUMMA_TRMM_L) {
+          const bool opupper = is_u(op.uplo) != is_t(op.trans);            // op(T) upper: rows <= contraction index
+          if (opupper) mhi = std::min<int64_t>(m, k1); else mlo = k0;
+        } else if (op.kind == SUMMA_TRMM_R) {
+          const bool opupper = is_u(op.uplo) != is_t(op.trans);            // op(T) upper: columns >= contraction index
+          if (opupper) nlo = std::max<int64_t>(n0, k0); else nhi = std::min<int64_t>(n1, k1);
+        }
+        const bool first = (s == 0 && q == 0);
+        const double bq = (first && !zero_first) ? beta : 1.0;
+        auto product = [&](int64_t r0, int64_t r1, int64_t c0, int64_t c1, int ctri) -> int {
+          if (r1 <= r0 || c1 <= c0) return CAP_OK;
+          GemmParams p{};
+          p.A = l_by_col ? Lq + r0 : Lq + r0 * ldlq; p.lda = ldlq;
+          p.B = r_by_col ? Rq + (c0 - n0) : Rq + (c0 - n0) * ldrq; p.ldb = ldrq;
+          p.C = S + r0 + c0 * lds; p.Cin = p.C; p.ldc = lds; p.ldcin = lds;
+          p.M = (int)(r1 - r0); p.N = (int)(c1 - c0); p.K = (int)kc; p.alpha = op.alpha; p.beta = bq; p.c_tri = ctri;
+          return gemm_launch(h, p, !l_by_col, r_by_col, -1);
+        };
+        if (op.c_tri == CTRI_UPPER) {          // only rows <= columns of the local block: a rectangle above the half's square + the square
+          CAP_TRY(product(0, std::min<int64_t>(m, nlo), nlo, nhi, CTRI_FULL));
+          CAP_TRY(product(nlo, std::min<int64_t>(m, nhi), nlo, nhi, CTRI_UPPER));
+        } else if (op.c_tri == CTRI_LOWER) {
+          CAP_TRY(product(nlo, std::min<int64_t>(m, nhi), nlo, nhi, CTRI_LOWER));
+          CAP_TRY(product(std::min<int64_t>(m, nhi), m, nlo, nhi, CTRI_FULL));
+        } else {
+          CAP_TRY(product(mlo, mhi, nlo, nhi, CTRI_FULL));
+        }
+        CUDA_TRY(cudaEventRecord(h->ev_sfree[bufi], ms));
+        used[bufi] = true;
+      }
+    }
+    if (!direct && c > 1) {                    // collect (summa.hpp:236) of this half beside the products of the next one
+      CUDA_TRY(cudaEventRecord(h->ev_shalf, ms));
+      StreamScope scope(h, cs, 0);
+      CUDA_TRY(cudaStreamWaitEvent(cs, h->ev_shalf, 0));
+      if (lds == m) { CAP_TRY(cap_allreduce_sum(h, g->depth, S + n0 * lds, m * (n1 - n0))); }
+      else for (int64_t col = n0; col < n1; ++col) CAP_TRY(cap_allreduce_sum(h, g->depth, S + col * lds, m));
+      CUDA_TRY(cudaEventRecord(h->ev_sred[hf], cs));
+    }
+  }
+  if (!direct) {
+    if (c > 1) for (int hf = 0; hf < nh; ++hf) CUDA_TRY(cudaStreamWaitEvent(ms, h->ev_sred[hf], 0));
+    CAP_TRY(axpby2d(h, C, ldc, S, lds, m, n, 1.0, beta, op.c_tri));          // C = beta*C + S (summa.hpp:32-35,153)
+  }
+  return CAP_OK;
+}
+
 // C_loc = alpha * sum over panels (left operand received along the row) x (right operand received along the
 // column) + beta * C_loc.  L is lr x lc, R is rr x rc as stored (any leading dimension); k = local contraction length.
 static int summa_core(cap_handle_t h, cap_grid_t g, SummaOp op, int64_t m, int64_t n, int64_t k,
@@ -155,21 +297,7 @@ static int summa_core(cap_handle_t h, cap_grid_t g, SummaOp op, int64_t m, int64
     const int64_t k0 = std::min<int64_t>(k, g->z * kz), k1 = std::min<int64_t>(k, k0 + kz);
     CAP_TRY(summa_local(h, op, m, n, k, k0, k1, L, ldl, R, ldr, direct ? beta : 0.0, S, lds));
   } else {
-    const int steps = d / c;
-    for (int s = 0; s < steps; ++s) {
-      const int kp = g->z + s * c;
-      const double *Lb, *Rb;
-      // left operand: owner x == kp broadcasts along its row (summa.hpp:185); right operand: y == kp along its column (:193)
-      if (g->x == kp) { CAP_TRY(contiguous(h, CAP_WS_SUMMA_A, L, ldl, lr, lc, &Lb)); }
-      else { double* w; CAP_TRY(cap_workspace(h, CAP_WS_SUMMA_A, (size_t)lr * lc * sizeof(double), &w)); Lb = w; }
-      CAP_TRY(cap_bcast(h, g->row, const_cast<double*>(Lb), lr * lc, kp));
-      if (g->y == kp) { CAP_TRY(contiguous(h, CAP_WS_SUMMA_B, R, ldr, rr, rc, &Rb)); }
-      else { double* w; CAP_TRY(cap_workspace(h, CAP_WS_SUMMA_B, (size_t)rr * rc * sizeof(double), &w)); Rb = w; }
-      CAP_TRY(cap_bcast(h, g->column, const_cast<double*>(Rb), rr * rc, kp));
-      const int64_t ldlb = (Lb == L) ? ldl : lr, ldrb = (Rb == R) ? ldr : rr;
-      const double b = (s == 0) ? (direct ? beta : 0.0) : 1.0;
-      CAP_TRY(summa_local(h, op, m, n, k, 0, k, Lb, ldlb, Rb, ldrb, b, S, lds));
-    }
+    return summa_pipelined(h, g, op, m, n, k, L, ldl, lr, lc, R, ldr, rr, rc, beta, C, ldc, S, lds, direct);
   }
   if (!direct) {
     if (c > 1) { CAP_TRY(cap_allreduce_sum(h, g->depth, S, m * n)); }       // collect (summa.hpp:236)

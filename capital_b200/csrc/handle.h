@@ -12,7 +12,7 @@ enum { CAP_WS_GEMM_SPLITK = 0, CAP_WS_TRI = 1, CAP_WS_PANEL = 2, CAP_WS_FACTOR =
        CAP_WS_GEMM_SPLITK2 = 18,                                                               // split-K partials of launches on the panel stream (bank 1)
        CAP_WS_POTRF1D = 19,                                                                    // look-ahead Cholesky: inverse block, row panels (double-buffered)
        CAP_WS_GEMM_SPLITK3 = 20,                                                               // split-K partials of launches on the row stream (bank 2)
-       CAP_WS_SLOTS = 21 };
+       CAP_WS_SLOTS = 21 };   // (CAP_WS_SUMMA_A: chunked left operand; CAP_WS_SUMMA_B: two right-operand chunk buffers)
 
 struct cap_ws_slot { void* ptr = nullptr; size_t bytes = 0; };
 
@@ -56,6 +56,9 @@ struct cap_handle_s {
   uint32_t* sig_scratch = nullptr;    // one word per signalling stream: the value a 4-byte peer copy carries
   struct cap_comm_s* peer_failed_comm = nullptr;   // CUDA IPC mapping failed on this communicator: do not retry every call
   int lookahead_grid_mult = 64;       // tile-engine grid multiplier of the trailing update beside a chain (0 = keep the persistent grid)
+  // chunked SUMMA (grid_algs.cuh): broadcasts / depth all-reduce on their own stream beside the local products
+  cudaStream_t summa_stream = nullptr;
+  cudaEvent_t ev_sready[2] = {}, ev_sfree[2] = {}, ev_shalf = nullptr, ev_sred[2] = {}, ev_sstart = nullptr;
   int lookahead_stair = 1;            // trailing update of the asynchronous schedule as ONE staircase launch (0 = a gemm + a syrk per run of blocks)
   int grid_mult = 1;                  // tile engine: CTAs per SM worth of grid (1 = persistent, one CTA per SM)
   int ws_bank = 0;                    // which split-K workspace slot gemm launches use (1 while launching on the panel stream)

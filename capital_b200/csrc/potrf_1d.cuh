@@ -69,11 +69,6 @@ __global__ void assemble_row_panel_kernel(double* __restrict__ Rrow, const doubl
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n2; i += (int64_t)gridDim.x * blockDim.x) dst[i] = src[i];
 }
 
-struct StreamScope {   // every helper in this file launches on h->stream: switch it (and the split-K workspace bank) for a scope
-  cap_handle_t h; cudaStream_t saved; int saved_bank;
-  StreamScope(cap_handle_t h_, cudaStream_t s, int bank) : h(h_), saved(h_->stream), saved_bank(h_->ws_bank) { h->stream = s; h->ws_bank = bank; }
-  ~StreamScope() { h->stream = saved; h->ws_bank = saved_bank; }
-};
 struct SmCapScope {
   cap_handle_t h; int saved;
   SmCapScope(cap_handle_t h_, int cap) : h(h_), saved(h_->num_sms) { if (cap > 0 && cap < saved) h->num_sms = cap; }

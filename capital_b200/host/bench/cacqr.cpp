@@ -13,7 +13,7 @@ int main(int argc, char** argv) {
   using qr_type = qr::cacqr<qr::policy::cacqr::Serialize, qr::policy::cacqr::SaveIntermediates>;
   using ci_type = cholesky::cholinv<cholesky::policy::cholinv::Serialize, cholesky::policy::cholinv::SaveIntermediates, cholesky::policy::cholinv::ReplicateComp>;
   for (U i = rep_start; i <= rep_end; ++i) {
-    topo::rect RectTopo(i, layout, num_chunks);
+    topo::rect RectTopo(MPI_COMM_WORLD, i, layout, num_chunks);
     MatrixType A(num_columns, num_rows, RectTopo.c, RectTopo.d);
     for (U j = bc_start; j <= bc_end; ++j) {
       ci_type::info<T, U> ci_pack(complete_inv, split, j, 'U');

@@ -10,7 +10,7 @@ int main(int argc, char** argv) {
   const U num_rows = atoll(argv[1]), rep_div = atoll(argv[2]); const bool complete_inv = atoi(argv[3]); const U split = atoll(argv[4]);
   const long bcMultiplier = atol(argv[5]); const size_t layout = atoi(argv[6]), num_chunks = atoi(argv[7]), num_iter = atoi(argv[8]);
   using cholesky_type = cholesky::cholinv<cholesky::policy::cholinv::Serialize, cholesky::policy::cholinv::SaveIntermediates, cholesky::policy::cholinv::ReplicateComp>;
-  topo::square SquareTopo(benchutil::grid_depth(rt.size(), rep_div), layout, num_chunks);
+  topo::square SquareTopo(MPI_COMM_WORLD, benchutil::grid_depth(rt.size(), rep_div), layout, num_chunks);
   MatrixType A(num_rows, num_rows, SquareTopo.d, SquareTopo.d);
   A.distribute_symmetric(SquareTopo.x, SquareTopo.y, SquareTopo.d, SquareTopo.d, rt.rank() / SquareTopo.c, true);
   cholesky_type::info<T, U> pack(complete_inv, split, bcMultiplier, 'U');

@@ -24,6 +24,15 @@ int main(int argc, char** argv) {
     if (rt.rank() == 0) std::cout << "total time - " << sec << "   # " << n * n * n / 3. / sec * 1e-12 << " TFLOP/s (N^3/3) on " << rt.size()
                                   << " GPU(s), block columns of " << nb << " dealt 1-D" << std::endl;
   }
+  if (getenv("CAPITAL_B200_VALIDATE") && rt.size() == 1) {   // ||R^T R - A||_F / ||A||_F over the upper triangle (test/cholesky/validate.hpp:7-30)
+    double* Rm = nullptr; double res = -1;
+    capital::check(cap_malloc((void**)&Rm, bytes), "cap_malloc");
+    capital::check(cap_copy2d(rt.handle(), Rm, N, A, N, N, N, 3), "cap_copy2d");          // R with an explicit zero lower triangle
+    topo::square One(MPI_COMM_WORLD, 1);
+    capital::check(cap_validate_cholinv(rt.handle(), One.grid, N, A0, N, Rm, N, &res), "cap_validate_cholinv");
+    std::cout << "residual ||R^T R - A||_F / ||A||_F (upper) - " << res << std::endl;
+    cap_free(Rm);
+  }
   int info = 0; cap_get_info(rt.handle(), &info);
   cap_free(A0); cap_free(A);
   if (info != 0) { std::cerr << "potrf info = " << info << std::endl; return 1; }

@@ -8,7 +8,7 @@ int main(int argc, char** argv) {
   auto& rt = capital::runtime::get();
   const U M = atoll(argv[1]), N = atoll(argv[2]), K = atoll(argv[3]), cdiv = atoll(argv[4]);
   const size_t layout = atoi(argv[5]), num_chunks = atoi(argv[6]), iters = atoi(argv[7]);
-  topo::square SquareTopo(benchutil::grid_depth(rt.size(), cdiv), layout, num_chunks);
+  topo::square SquareTopo(MPI_COMM_WORLD, benchutil::grid_depth(rt.size(), cdiv), layout, num_chunks);
   MatrixTypeR matA(K, M, SquareTopo.d, SquareTopo.d), matB(N, K, SquareTopo.d, SquareTopo.d), matC(N, M, SquareTopo.d, SquareTopo.d);
   blas::ArgPack_gemm<T> blasArgs(blas::Order::AblasColumnMajor, blas::Transpose::AblasNoTrans, blas::Transpose::AblasNoTrans, 1., 0.);
   matA.distribute_random(SquareTopo.x, SquareTopo.y, SquareTopo.d, SquareTopo.d, rt.rank() / SquareTopo.c);

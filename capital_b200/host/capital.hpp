@@ -16,7 +16,10 @@
 // through pack()/unpack()); one process per GPU, ranks come from torchrun-style environment variables and
 // the NCCL id is exchanged through a file under /tmp (one node).  Header-only; link libcapital_b200.so.
 #pragma once
+#include <fcntl.h>
 #include <unistd.h>
+
+#include <ctime>
 
 #include <cassert>
 #include <chrono>
@@ -79,20 +82,37 @@ private:
     check(cap_malloc((void**)&gather_, 8 * (size_t)size_), "cap_malloc");
     if (size_ > 1) {
       char id[128];
-      const std::string path = "/tmp/capital_b200_ncclid_" + std::string(getenv("MASTER_PORT") ? getenv("MASTER_PORT") : "0") + "_" +
-                               std::string(getenv("TORCHELASTIC_RUN_ID") ? getenv("TORCHELASTIC_RUN_ID") : "run");
+      // One file per LAUNCH: the name carries the launcher's pid (the same torchrun agent forks every rank) next to the
+      // port, rank 0 creates it with O_EXCL and mode 0600 after removing any left-over, writes a header with its own pid
+      // and start time, and the other ranks accept only a complete file whose header is younger than their own start.
+      const char* port = getenv("MASTER_PORT");
+      const std::string path = "/tmp/capital_b200_ncclid_" + std::string(port ? port : "0") + "_" + std::to_string((long)getppid()) + "_" +
+                               std::to_string((long)getuid());
+      struct { long long magic, stamp; char id[128]; } rec;
+      const long long now_s = (long long)time(nullptr);
       if (rank_ == 0) {
         check(cap_comm_unique_id(id), "cap_comm_unique_id");
+        unlink(path.c_str());
         const std::string tmp = path + ".tmp";
-        FILE* f = fopen(tmp.c_str(), "wb");
-        if (!f || fwrite(id, 1, 128, f) != 128) throw std::runtime_error("cannot write " + tmp);
-        fclose(f);
-        rename(tmp.c_str(), path.c_str());
+        unlink(tmp.c_str());
+        const int fd = open(tmp.c_str(), O_WRONLY | O_CREAT | O_EXCL, 0600);
+        if (fd < 0) throw std::runtime_error("cannot create " + tmp);
+        rec.magic = 0x43415042323030LL; rec.stamp = now_s; memcpy(rec.id, id, 128);
+        const bool ok = write(fd, &rec, sizeof rec) == (ssize_t)sizeof rec;
+        close(fd);
+        if (!ok || rename(tmp.c_str(), path.c_str()) != 0) throw std::runtime_error("cannot write " + path);
       } else {
-        FILE* f = nullptr;
-        for (int tries = 0; tries < 6000 && !(f = fopen(path.c_str(), "rb")); ++tries) std::this_thread::sleep_for(std::chrono::milliseconds(10));
-        if (!f || fread(id, 1, 128, f) != 128) throw std::runtime_error("cannot read " + path);
-        fclose(f);
+        bool got = false;
+        for (int tries = 0; tries < 12000 && !got; ++tries) {          // two minutes, then an error instead of a hang
+          FILE* f = fopen(path.c_str(), "rb");
+          if (f) {
+            got = fread(&rec, 1, sizeof rec, f) == sizeof rec && rec.magic == 0x43415042323030LL && rec.stamp >= now_s - 600;
+            fclose(f);
+          }
+          if (!got) std::this_thread::sleep_for(std::chrono::milliseconds(10));
+        }
+        if (!got) throw std::runtime_error("no NCCL id from rank 0 within 120 s (" + path + ")");
+        memcpy(id, rec.id, 128);
       }
       check(cap_comm_init_rank(&world_, id, size_, rank_), "cap_comm_init_rank");
       barrier();
@@ -107,7 +127,18 @@ private:
 
 inline cap_handle_t handle() { return runtime::get().handle(); }
 
+// What stands where the reference passes an MPI communicator (topology.h:18,69): the ranks of the runtime.
+struct world_t {};
+constexpr world_t WORLD{};
+
 }  // namespace capital
+
+// Code written against the reference says topo::square(MPI_COMM_WORLD, c, layout, num_chunks): when no MPI header is in
+// sight these two names make that line compile unchanged (a build with a real <mpi.h> passes capital::WORLD instead).
+#if !defined(MPI_COMM_WORLD) && !defined(CAPITAL_B200_NO_MPI_NAMES)
+using MPI_Comm = capital::world_t;
+constexpr MPI_Comm MPI_COMM_WORLD{};
+#endif
 
 // ------------------------------------------------------------------------------------------ blas::engine
 namespace blas {
@@ -187,14 +218,17 @@ namespace topo {
 // c x d x d grid (topology.h:67-143, layout 0); P = c*d*d with d % c == 0 or d == 1
 class square {
 public:
-  explicit square(size_t c_, size_t layout_ = 0, size_t num_chunks_ = 0) : layout(layout_), num_chunks(num_chunks_) {
+  // topology.h:69: square(MPI_Comm comm, size_t c, size_t layout = 0, size_t num_chunks = 0).  layout 0 / 1 are the
+  // reference's two rank orders; num_chunks is the number of pieces per panel of the pipelined SUMMA (0 = automatic).
+  square(capital::world_t, size_t c_, size_t layout_ = 0, size_t num_chunks_ = 0) : layout(layout_), num_chunks(num_chunks_) {
     auto& rt = capital::runtime::get();
     rank = rt.rank(); size = rt.size();
-    capital::check(cap_grid_create(rt.world(), (int)c_, &grid), "cap_grid_create");
+    capital::check(cap_grid_create2(rt.world(), (int)c_, (int)layout_, (int)num_chunks_, &grid), "cap_grid_create");
     int ci, di, xi, yi, zi;
     cap_grid_info(grid, &ci, &di, &xi, &yi, &zi);
     c = ci; d = di; x = xi; y = yi; z = zi;
   }
+  explicit square(size_t c_, size_t layout_ = 0, size_t num_chunks_ = 0) : square(capital::WORLD, c_, layout_, num_chunks_) {}
   ~square() { cap_grid_destroy(grid); }
   square(const square&) = delete;
   cap_grid_t grid = nullptr;
@@ -207,16 +241,18 @@ public:
 // grids (d % c == 0 or d == 1) are what cap_cacqr_factor_3d generalises to.
 class rect {
 public:
-  explicit rect(size_t c_, size_t layout_ = 0, size_t num_chunks_ = 0) : layout(layout_), num_chunks(num_chunks_) {
+  // topology.h:18: rect(MPI_Comm comm, size_t c, size_t layout = 0, size_t num_chunks = 0)
+  rect(capital::world_t, size_t c_, size_t layout_ = 0, size_t num_chunks_ = 0) : layout(layout_), num_chunks(num_chunks_) {
     auto& rt = capital::runtime::get();
     rank = rt.rank(); size = rt.size();
     if (c_ <= 1) { c = 1; d = size; x = 0; y = rank; z = 0; return; }
     if (c_ * c_ * c_ != (size_t)size) throw std::runtime_error("topo::rect: c > 1 needs c^3 ranks here; use topo::square(c) for c x d x d grids");
-    capital::check(cap_grid_create(rt.world(), (int)c_, &grid), "cap_grid_create");
+    capital::check(cap_grid_create2(rt.world(), (int)c_, (int)layout_, (int)num_chunks_, &grid), "cap_grid_create");
     int ci, di, xi, yi, zi;
     cap_grid_info(grid, &ci, &di, &xi, &yi, &zi);
     c = ci; d = di; x = xi; y = yi; z = zi;
   }
+  explicit rect(size_t c_, size_t layout_ = 0, size_t num_chunks_ = 0) : rect(capital::WORLD, c_, layout_, num_chunks_) {}
   ~rect() { if (grid) cap_grid_destroy(grid); }
   rect(const rect&) = delete;
   cap_grid_t grid = nullptr;
@@ -244,7 +280,7 @@ public:
   }
   // injection constructor (matrix.hpp:53-74): wrap a caller-owned device pointer
   matrix(ScalarT* data, DimensionT dimensionX, DimensionT dimensionY, DimensionT globalPgridX, DimensionT globalPgridY)
-      : data_(data), owned_(false), dimX_(dimensionX), dimY_(dimensionY), gX_(dimensionX * globalPgridX), gY_(dimensionY * globalPgridY) {}
+      : data_(data), owned_(false), dimX_(dimensionX), dimY_(dimensionY), gX_(dimensionX * globalPgridX), gY_(dimensionY * globalPgridY), ld_(dimensionY) {}
   matrix(const matrix& rhs) { copy_from(rhs); }
   matrix(matrix&& rhs) noexcept { steal(rhs); }
   matrix& operator=(const matrix& rhs) { if (this != &rhs) { _destroy_(); copy_from(rhs); } return *this; }
@@ -254,52 +290,123 @@ public:
   void _register_(DimensionT globalDimensionX, DimensionT globalDimensionY, int64_t globalPgridX, int64_t globalPgridY) {
     _destroy_();
     gX_ = globalDimensionX; gY_ = globalDimensionY;
-    dimX_ = (globalDimensionX + globalPgridX - 1) / globalPgridX;     // ceil: zero padding past the edge (matrix.hpp:8-11)
+    dimX_ = (globalDimensionX + globalPgridX - 1) / globalPgridX;     // ceil: zero padding past the edge (matrix.hpp:142-150)
     dimY_ = (globalDimensionY + globalPgridY - 1) / globalPgridY;
+    ld_ = dimY_;
+    _fill_();
+  }
+  // matrix.hpp:127-139: second half of the two-part construction -- allocate (zero-filled) unless a pointer was injected
+  void _fill_() {
+    if (data_ || dimX_ * dimY_ == 0) return;
     capital::check(cap_malloc((void**)&data_, sizeof(double) * (size_t)dimX_ * dimY_), "cap_malloc");
     capital::check(cap_memset_async(capital::handle(), data_, 0, sizeof(double) * (size_t)dimX_ * dimY_), "cap_memset_async");
     owned_ = true;
   }
-  void _destroy_() { if (owned_ && data_) cap_free(data_); data_ = nullptr; owned_ = false; }
+  void _destroy_() {
+    if (saved_) _derestrict_();
+    if (owned_ && data_) cap_free(data_);
+    if (scratch_) cap_free(scratch_);
+    if (pad_) cap_free(pad_);
+    data_ = scratch_ = pad_ = nullptr; owned_ = false;
+  }
+  // matrix.hpp:172-180: work on the sub-block [startX, endX) x [startY, endY) of the local block.  Here a restricted
+  // matrix is a (pointer, leading dimension) view: data() moves, ld() stays, the local dimensions shrink.
+  void _restrict_(DimensionT startX, DimensionT endX, DimensionT startY, DimensionT endY) {
+    assert(!saved_ && startX >= 0 && endX <= dimX_ && startY >= 0 && endY <= dimY_);
+    sv_data_ = data_; sv_scratch_ = scratch_; sv_dimX_ = dimX_; sv_dimY_ = dimY_; saved_ = true;
+    data_ += startY + startX * ld_;
+    if (scratch_) scratch_ += startY + startX * ld_;
+    dimX_ = endX - startX; dimY_ = endY - startY;
+  }
+  void _derestrict_() {
+    if (!saved_) return;
+    data_ = sv_data_; scratch_ = sv_scratch_; dimX_ = sv_dimX_; dimY_ = sv_dimY_; saved_ = false;
+  }
 
+  ScalarT*& data() { return data_; }
   ScalarT* data() const { return data_; }
+  // matrix.h:41-44: second (and, for triangular structures, third) buffer of the same size for one-to-all / all-to-one
+  // exchanges; device memory, allocated on first use
+  ScalarT*& scratch() { if (!scratch_) alloc_like(&scratch_); return scratch_; }
+  ScalarT* scratch() const { return scratch_; }
+  ScalarT*& pad() { if (!pad_) alloc_like(&pad_); return pad_; }
+  ScalarT* pad() const { return pad_; }
+  void swap() { ScalarT* t = data(); data() = scratch(); scratch() = t; }          // matrix.h:55
+  void swap_pad() { ScalarT* t = scratch(); scratch() = pad(); pad() = t; }        // matrix.h:56
+  DimensionT ld() const { return ld_; }                                            // leading dimension of data() (column-major)
   DimensionT num_elems() const { return dimX_ * dimY_; }
+  DimensionT num_elems(DimensionT rangeX, DimensionT rangeY) const { return rangeX * rangeY; }
   DimensionT num_rows_local() const { return dimY_; }
   DimensionT num_columns_local() const { return dimX_; }
   DimensionT num_rows_global() const { return gY_; }
   DimensionT num_columns_global() const { return gX_; }
+  DimensionT offset_local(DimensionT coordX, DimensionT coordY, size_t = 0) const { return coordY + coordX * ld_; }
+  void set_num_rows_local(DimensionT v) { dimY_ = v; }
+  void set_num_columns_local(DimensionT v) { dimX_ = v; }
+  void set_num_rows_global(DimensionT v) { gY_ = v; }
+  void set_num_columns_global(DimensionT v) { gX_ = v; }
 
-  // structure.hpp:106-129: element t of the local block (column by column) = t-th drand48 value after srand48(key)
-  void distribute_random(int64_t, int64_t, int64_t, int64_t, int64_t key) {
-    capital::check(cap_fill_random(capital::handle(), data_, dimY_, dimY_, dimX_, key), "cap_fill_random");
+  // Edge padding as in the reference (structure.hpp:42-43,72-73,110-111): when the grid does not divide a global dimension,
+  // the ranks past the remainder hold one zero row / column at the end of their block and draw one value fewer per column.
+  DimensionT pad_len(DimensionT dim, DimensionT global, int64_t local_p, int64_t grid_p) const {
+    return ((global % grid_p != 0) && ((dim - 1) * grid_p + local_p >= global)) ? dim - 1 : dim;
+  }
+  // structure.hpp:106-129: element t of the UNPADDED local block (column by column) = t-th drand48 value after srand48(key)
+  void distribute_random(int64_t localPgridX, int64_t localPgridY, int64_t globalPgridX, int64_t globalPgridY, int64_t key) {
+    const DimensionT px = pad_len(dimX_, gX_, localPgridX, globalPgridX), py = pad_len(dimY_, gY_, localPgridY, globalPgridY);
+    zero_all();
+    capital::check(cap_fill_random(capital::handle(), data_, ld_, py, px, key), "cap_fill_random");
   }
   // structure.hpp:69-103: a(gy,gx) seeded by max + N*min, + N on the diagonal when diagonallyDominant
   void distribute_symmetric(int64_t localPgridX, int64_t localPgridY, int64_t globalPgridX, int64_t globalPgridY, int64_t, bool diagonallyDominant) {
-    capital::check(cap_fill_symmetric(capital::handle(), data_, dimY_, dimY_, dimX_, localPgridX, localPgridY, globalPgridX, globalPgridY,
+    const DimensionT px = pad_len(dimX_, gX_, localPgridX, globalPgridX), py = pad_len(dimY_, gY_, localPgridY, globalPgridY);
+    zero_all();
+    capital::check(cap_fill_symmetric(capital::handle(), data_, ld_, py, px, localPgridX, localPgridY, globalPgridX, globalPgridY,
                                       gY_, diagonallyDominant ? 1 : 0), "cap_fill_symmetric");
+  }
+  // structure.hpp:37-66: val where local row == local column on the processes of the grid diagonal, zero elsewhere
+  void distribute_identity(int64_t localPgridX, int64_t localPgridY, int64_t globalPgridX, int64_t globalPgridY, ScalarT val = 1.) {
+    const DimensionT px = pad_len(dimX_, gX_, localPgridX, globalPgridX), py = pad_len(dimY_, gY_, localPgridY, globalPgridY);
+    zero_all();
+    if (localPgridX == localPgridY) capital::check(cap_fill_diagonal(capital::handle(), data_, ld_, py < px ? py : px, val), "cap_fill_diagonal");
   }
   std::vector<double> to_host() const {
     std::vector<double> out((size_t)dimX_ * dimY_);
-    capital::check(cap_d2h_async(capital::handle(), out.data(), data_, sizeof(double) * out.size()), "cap_d2h_async");
+    if (ld_ == dimY_) capital::check(cap_d2h_async(capital::handle(), out.data(), data_, sizeof(double) * out.size()), "cap_d2h_async");
+    else for (DimensionT c = 0; c < dimX_; ++c)
+      capital::check(cap_d2h_async(capital::handle(), out.data() + (size_t)c * dimY_, data_ + (size_t)c * ld_, sizeof(double) * dimY_), "cap_d2h_async");
     capital::check(cap_synchronize(capital::handle()), "cap_synchronize");
     return out;
   }
 
 private:
+  void alloc_like(ScalarT** p) {
+    const size_t n = (size_t)(saved_ ? sv_dimX_ : dimX_) * ld_;
+    capital::check(cap_malloc((void**)p, sizeof(double) * n), "cap_malloc");
+    capital::check(cap_memset_async(capital::handle(), *p, 0, sizeof(double) * n), "cap_memset_async");
+  }
+  void zero_all() {
+    if (ld_ == dimY_) capital::check(cap_memset_async(capital::handle(), data_, 0, sizeof(double) * (size_t)dimX_ * dimY_), "cap_memset_async");
+    else capital::check(cap_axpby2d(capital::handle(), data_, ld_, data_, ld_, dimY_, dimX_, 0.0, 0.0), "cap_axpby2d");
+  }
   void copy_from(const matrix& rhs) {
-    dimX_ = rhs.dimX_; dimY_ = rhs.dimY_; gX_ = rhs.gX_; gY_ = rhs.gY_; owned_ = false; data_ = nullptr;
+    dimX_ = rhs.dimX_; dimY_ = rhs.dimY_; gX_ = rhs.gX_; gY_ = rhs.gY_; ld_ = rhs.dimY_; owned_ = false; data_ = scratch_ = pad_ = nullptr; saved_ = false;
     if (!rhs.data_) return;
     capital::check(cap_malloc((void**)&data_, sizeof(double) * (size_t)dimX_ * dimY_), "cap_malloc");
     owned_ = true;
-    capital::check(cap_copy2d(capital::handle(), data_, dimY_, rhs.data_, dimY_, dimY_, dimX_, 0), "cap_copy2d");
+    capital::check(cap_copy2d(capital::handle(), data_, ld_, rhs.data_, rhs.ld_, dimY_, dimX_, 0), "cap_copy2d");
   }
   void steal(matrix& rhs) {
-    data_ = rhs.data_; owned_ = rhs.owned_; dimX_ = rhs.dimX_; dimY_ = rhs.dimY_; gX_ = rhs.gX_; gY_ = rhs.gY_;
-    rhs.data_ = nullptr; rhs.owned_ = false;
+    data_ = rhs.data_; scratch_ = rhs.scratch_; pad_ = rhs.pad_; owned_ = rhs.owned_; dimX_ = rhs.dimX_; dimY_ = rhs.dimY_; gX_ = rhs.gX_; gY_ = rhs.gY_; ld_ = rhs.ld_;
+    saved_ = rhs.saved_; sv_data_ = rhs.sv_data_; sv_scratch_ = rhs.sv_scratch_; sv_dimX_ = rhs.sv_dimX_; sv_dimY_ = rhs.sv_dimY_;
+    rhs.data_ = rhs.scratch_ = rhs.pad_ = nullptr; rhs.owned_ = false; rhs.saved_ = false;
   }
-  ScalarT* data_ = nullptr;
+  ScalarT *data_ = nullptr, *scratch_ = nullptr, *pad_ = nullptr;
   bool owned_ = false;
-  DimensionT dimX_ = 0, dimY_ = 0, gX_ = 0, gY_ = 0;
+  DimensionT dimX_ = 0, dimY_ = 0, gX_ = 0, gY_ = 0, ld_ = 0;
+  bool saved_ = false;                       // _restrict_ state
+  ScalarT *sv_data_ = nullptr, *sv_scratch_ = nullptr;
+  DimensionT sv_dimX_ = 0, sv_dimY_ = 0;
 };
 
 // ------------------------------------------------------------------------------------------ matmult::summa
@@ -313,21 +420,21 @@ public:
     const int64_t m = ta ? A.num_columns_local() : A.num_rows_local(), n = tb ? B.num_rows_local() : B.num_columns_local();
     const int64_t k = ta ? A.num_rows_local() : A.num_columns_local();
     capital::check(cap_summa_gemm(capital::handle(), ci.grid, blas::chr(p.transposeA), blas::chr(p.transposeB), m, n, k, p.alpha,
-                                  A.data(), A.num_rows_local(), B.data(), B.num_rows_local(), p.beta, C.data(), C.num_rows_local()), "cap_summa_gemm");
+                                  A.data(), A.ld(), B.data(), B.ld(), p.beta, C.data(), C.ld()), "cap_summa_gemm");
   }
   // trmm (summa.hpp:47-83): A triangular, B rectangular and overwritten
   template <typename MA, typename MB, typename CommType>
   static void invoke(MA& A, MB& B, CommType&& ci, blas::ArgPack_trmm<double>& p) {
     capital::check(cap_summa_trmm(capital::handle(), ci.grid, blas::chr(p.side), blas::chr(p.uplo), blas::chr(p.transposeA), blas::chr(p.diag),
-                                  B.num_rows_local(), B.num_columns_local(), p.alpha, A.data(), A.num_rows_local(), B.data(), B.num_rows_local()), "cap_summa_trmm");
+                                  B.num_rows_local(), B.num_columns_local(), p.alpha, A.data(), A.ld(), B.data(), B.ld()), "cap_summa_trmm");
   }
   // syrk (summa.hpp:86-96): the grid-transposed copy is made inside
   template <typename MS, typename MD, typename CommType>
   static void invoke(MS& A, MD& C, CommType&& ci, blas::ArgPack_syrk<double>& p) {
     const bool tr = p.transposeA == blas::Transpose::AblasTrans;
     capital::check(cap_summa_syrk(capital::handle(), ci.grid, blas::chr(p.uplo), blas::chr(p.transposeA), C.num_columns_local(),
-                                  tr ? A.num_rows_local() : A.num_columns_local(), p.alpha, A.data(), A.num_rows_local(), nullptr, 0, p.beta,
-                                  C.data(), C.num_rows_local()), "cap_summa_syrk");
+                                  tr ? A.num_rows_local() : A.num_columns_local(), p.alpha, A.data(), A.ld(), nullptr, 0, p.beta,
+                                  C.data(), C.ld()), "cap_summa_syrk");
   }
 };
 }  // namespace matmult
@@ -445,7 +552,7 @@ struct validate {
   template <typename MatrixType, typename ArgType, typename CommType>
   static double residual(const MatrixType& A, ArgType& args, CommType&& ci) {
     double r = 0;
-    capital::check(cap_validate_cholinv(capital::handle(), ci.grid, A.num_rows_local(), A.data(), A.num_rows_local(),
+    capital::check(cap_validate_cholinv(capital::handle(), ci.grid, A.num_rows_local(), A.data(), A.ld(),
                                         args.R.data(), args.R.num_rows_local(), &r), "cap_validate_cholinv");
     return r;
   }

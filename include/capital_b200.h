@@ -102,6 +102,10 @@ int cap_copy2d(cap_handle_t h, double* dst, int64_t ldd, const double* src, int6
 int cap_pack_upper(cap_handle_t h, double* packed, const double* full, int64_t ld, int n);
 int cap_unpack_upper(cap_handle_t h, double* full, int64_t ld, const double* packed, int n, int zero_lower);
 int cap_axpby(cap_handle_t h, double* y, const double* x, int64_t count, double alpha, double beta);
+/* y(m x n, ldy) = alpha * x(m x n, ldx) + beta * y: the strided form (views of a larger local block) */
+int cap_axpby2d(cap_handle_t h, double* y, int64_t ldy, const double* x, int64_t ldx, int64_t m, int64_t n, double alpha, double beta);
+/* dst[i + i*ld] = value for i < n (rect::_distribute_identity, src/matrix/structure.hpp:37-66, on a zeroed block) */
+int cap_fill_diagonal(cap_handle_t h, double* dst, int64_t ld, int64_t n, double value);
 
 /* ---- generators (src/matrix/structure.hpp:69-129), bit-exact with glibc drand48 -------------- */
 int cap_fill_random(cap_handle_t h, double* dst, int64_t ld, int64_t rows, int64_t cols, long long key);
@@ -128,6 +132,10 @@ int cap_sendrecv(cap_handle_t h, cap_comm_t comm, const double* send, double* re
  * All dimensions below are LOCAL block dimensions; all calls are collective over the grid and stream-ordered. */
 typedef struct cap_grid_s* cap_grid_t;
 int cap_grid_create(cap_comm_t world, int c, cap_grid_t* grid);      /* world may be NULL for a single rank */
+/* topo::square(comm, c, layout, num_chunks) (src/util/topology.h:69): layout 0 or 1 = the two rank -> (x, y, z) orders of the
+ * reference; num_chunks = pieces per panel of the pipelined SUMMA (0 = chosen from the contraction length) */
+int cap_grid_create2(cap_comm_t world, int c, int layout, int num_chunks, cap_grid_t* grid);
+int cap_grid_set_chunks(cap_grid_t grid, int num_chunks);
 int cap_grid_destroy(cap_grid_t grid);
 int cap_grid_info(cap_grid_t grid, int* c, int* d, int* x, int* y, int* z);
 /* util::transpose (src/util/util.hpp:233-247): dst <- the block of the process at (y, x) in the same layer */

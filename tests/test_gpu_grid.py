@@ -74,11 +74,21 @@ def test_cpp_host_drivers():
     bindir = os.path.join(ROOT, "capital_b200", "host", "bin")
     if not os.path.exists(os.path.join(bindir, "cacqr")):
         pytest.skip("host drivers not built (python -m capital_b200.build)")
-    for cmd in (["cacqr", "2", "65536", "256", "1", "1", "1", "1", "0", "0", "0", "0", "1"],
-                ["cholinv", "2048", "1", "1", "1", "0", "0", "0", "1"],
-                ["summa_gemm", "1024", "768", "512", "1", "0", "0", "1"]):
-        out = subprocess.run([os.path.join(bindir, cmd[0])] + cmd[1:], capture_output=True, text=True, timeout=300)
+    import re
+    env = dict(os.environ, CAPITAL_B200_VALIDATE="1")
+    num = r"([0-9.eE+-]+)"
+    for cmd, n, patterns in (
+            (["cacqr", "2", "65536", "256", "1", "1", "1", "1", "0", "0", "0", "0", "1"], 256, [r"orthogonality .* - " + num + r"\s+residual", r"residual \|\|Q R - A.* - " + num]),
+            (["cholinv", "2048", "1", "1", "1", "0", "0", "0", "1"], 2048, [r"residual \|\|R\^T R - A.* - " + num]),
+            (["cholinv", "2048", "1", "0", "1", "-2", "1", "3", "1"], 2048, [r"residual \|\|R\^T R - A.* - " + num]),      # layout 1, num_chunks 3
+            (["potrf", "3000", "256", "1"], 3000, [r"residual \|\|R\^T R - A.* - " + num]),
+            (["summa_gemm", "1024", "768", "512", "1", "0", "0", "1"], 0, [])):
+        out = subprocess.run([os.path.join(bindir, cmd[0])] + cmd[1:], capture_output=True, text=True, timeout=300, env=env)
         assert out.returncode == 0 and "TFLOP/s" in out.stdout, out.stdout[-2000:] + out.stderr[-2000:]
+        for pat in patterns:                       # the reference's validators, printed by the driver: test/qr/validate.hpp, test/cholesky/validate.hpp
+            m = re.search(pat, out.stdout)
+            assert m, (pat, out.stdout[-1500:])
+            assert float(m.group(1)) <= 1e-13 * n, (cmd, m.group(0))
 
 
 @pytest.mark.parametrize("side,uplo,tr", [(s, u, t) for s in "LR" for u in "UL" for t in "NT"])
