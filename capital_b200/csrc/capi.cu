@@ -51,7 +51,10 @@ int cap_create(cap_handle_t* out, int device) {
   h->device = device;
   h->num_sms = prop.multiProcessorCount;
   if (const char* e = getenv("CAPITAL_B200_GRID_MULT")) h->grid_mult = std::max(1, atoi(e));   // probe switch: tile-engine grid = k x #SMs everywhere
-  if (const char* e = getenv("CAPITAL_B200_STAIR")) h->lookahead_stair = atoi(e);     // A/B switch: 0 = trailing update block run by block run
+  if (const char* e = getenv("CAPITAL_B200_STAIR")) h->lookahead_stair = atoi(e);
+  if (const char* e = getenv("CAPITAL_B200_SUMMA_PIPE")) h->summa_pipeline = atoi(e);           // A/B switches of the pipelined SUMMA
+  if (const char* e = getenv("CAPITAL_B200_SUMMA_RESERVE")) h->summa_reserve_sms = atoi(e);
+  if (const char* e = getenv("CAPITAL_B200_SUMMA_HALVES")) h->summa_halves = atoi(e);     // A/B switch: 0 = trailing update block run by block run
   CUDA_TRY(cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking));
   CUDA_TRY(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
   h->stream = h->own_stream;
@@ -915,6 +918,12 @@ struct StreamScope {   // the helpers launch on h->stream: switch it (and the sp
   cap_handle_t h; cudaStream_t saved; int saved_bank;
   StreamScope(cap_handle_t h_, cudaStream_t s, int bank) : h(h_), saved(h_->stream), saved_bank(h_->ws_bank) { h->stream = s; h->ws_bank = bank; }
   ~StreamScope() { h->stream = saved; h->ws_bank = saved_bank; }
+};
+
+struct SmCapScope {
+  cap_handle_t h; int saved;
+  SmCapScope(cap_handle_t h_, int cap) : h(h_), saved(h_->num_sms) { if (cap > 0 && cap < saved) h->num_sms = cap; }
+  ~SmCapScope() { h->num_sms = saved; }
 };
 
 #include "grid_algs.cuh"

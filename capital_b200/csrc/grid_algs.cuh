@@ -140,6 +140,8 @@ static int summa_local(cap_handle_t h, const SummaOp& op, int64_t m, int64_t n, 
   return trmm_impl(h, 'R', op.uplo, op.trans, op.diag, m, n, op.alpha, R, ldr, L, ldl, target, ldt, op.t_clean, false, beta);
 }
 
+__global__ void mask_cyclic_upper_kernel(double* __restrict__ A, int64_t lda, int len, int d, int x, int y);
+
 // d > 1: the panel loop of summa::distribute / collect with communication and computation overlapped -- the job of the
 // reference's num_chunks pipeline (summa.hpp:196-215 chunked MPI_Ibcast, :238-249 chunked MPI_Iallreduce).  Both operands
 // of a panel are cut along the CONTRACTION index into num_chunks pieces; piece q+1 travels (row broadcast of the left
@@ -176,10 +178,13 @@ static int summa_pipelined(cap_handle_t h, cap_grid_t g, const SummaOp& op, int6
   nq = (int)std::min<int64_t>(nq, std::max<int64_t>(1, k / 128));
   const int64_t kc_max = ((k + nq - 1) / nq + 127) / 128 * 128;
   nq = (int)((k + kc_max - 1) / kc_max);
-  const int nh = (c > 1 && n >= 256) ? 2 : 1;
+  const int nh = (c > 1 && n >= 256 && h->summa_halves) ? 2 : 1;
   const int64_t nh0 = nh == 2 ? ((n / 2 + 127) / 128) * 128 : n;       // columns of the first half
   double *Lbuf, *Rbuf;
-  CAP_TRY(cap_workspace(h, CAP_WS_SUMMA_A, (size_t)lr * lc * sizeof(double), &Lbuf));
+  // several panels: the left landing buffer alternates between two halves, so a panel's pieces never land on the pieces a
+  // product of the previous panel still reads (the panel before that is done: its products precede, on the compute
+  // stream, the ones whose completion the right-operand buffers already wait for)
+  CAP_TRY(cap_workspace(h, CAP_WS_SUMMA_A, (size_t)(steps > 1 ? 2 : 1) * lr * lc * sizeof(double), &Lbuf));
   const int64_t r_other = r_by_col ? rr : rc;                              // extent of R across the contraction index
   CAP_TRY(cap_workspace(h, CAP_WS_SUMMA_B, (size_t)2 * kc_max * r_other * sizeof(double), &Rbuf));
   const bool zero_first = tri || !direct;                                  // restricted products never write the whole of S
@@ -196,7 +201,7 @@ static int summa_pipelined(cap_handle_t h, cap_grid_t g, const SummaOp& op, int6
       for (int q = 0; q < nq; ++q, ++seq) {
         const int64_t k0 = (int64_t)q * kc_max, k1 = std::min<int64_t>(k, k0 + kc_max), kc = k1 - k0;
         const int bufi = seq & 1;
-        double* Lq = Lbuf + (l_by_col ? k0 * lr : k0 * lc);               // piece q of the left operand: lr x kc (ld lr) or kc x lc (ld kc)
+        double* Lq = Lbuf + (size_t)((hf * steps + s) & 1) * (steps > 1 ? lr * lc : 0) + (l_by_col ? k0 * lr : k0 * lc);   // piece q of the left operand: lr x kc (ld lr) or kc x lc (ld kc)
         const int64_t ldlq = l_by_col ? lr : kc;
         double* Rq = Rbuf + (size_t)bufi * kc_max * r_other;              // piece of the right operand restricted to the half's columns
         const int64_t rcols = n1 - n0;
@@ -232,6 +237,7 @@ static int summa_pipelined(cap_handle_t h, cap_grid_t g, const SummaOp& op, int6
         const double bq = (first && !zero_first) ? beta : 1.0;
         auto product = [&](int64_t r0, int64_t r1, int64_t c0, int64_t c1, int ctri) -> int {
           if (r1 <= r0 || c1 <= c0) return CAP_OK;
+          SmCapScope cap(h, h->summa_reserve_sms > 0 ? h->num_sms - h->summa_reserve_sms : 0);   // room for the NCCL kernels of the next piece
           GemmParams p{};
           p.A = l_by_col ? Lq + r0 : Lq + r0 * ldlq; p.lda = ldlq;
           p.B = r_by_col ? Rq + (c0 - n0) : Rq + (c0 - n0) * ldrq; p.ldb = ldrq;
@@ -297,7 +303,44 @@ static int summa_core(cap_handle_t h, cap_grid_t g, SummaOp op, int64_t m, int64
     const int64_t k0 = std::min<int64_t>(k, g->z * kz), k1 = std::min<int64_t>(k, k0 + kz);
     CAP_TRY(summa_local(h, op, m, n, k, k0, k1, L, ldl, R, ldr, direct ? beta : 0.0, S, lds));
   } else {
-    return summa_pipelined(h, g, op, m, n, k, L, ldl, lr, lc, R, ldr, rr, rc, beta, C, ldc, S, lds, direct);
+    if (op.kind != SUMMA_GEMM && !op.t_clean) {
+      // the pipelined products multiply pieces of the triangular operand as general panels: materialise its zero triangle
+      // once (global row <= global column for upper; the local triangle for lower)
+      const bool left = op.kind == SUMMA_TRMM_L;
+      const int64_t nt = left ? m : n;
+      const double* T = left ? L : R; const int64_t ldt = left ? ldl : ldr;
+      double* tc;
+      CAP_TRY(cap_workspace(h, CAP_WS_SUMMA_T, (size_t)nt * nt * sizeof(double), &tc));
+      if (is_u(op.uplo)) {
+        CAP_TRY(copy2d(h, tc, nt, T, ldt, nt, nt, 0));
+        dim3 gl((unsigned)((nt + 255) / 256), (unsigned)nt);
+        // op(T) = T^T: the caller hands in the grid-transposed block (util::transpose, as cholinv.hpp:116-118 does), i.e. the
+        // block of the process at (y, x)
+        const bool tr = is_t(op.trans);
+        mask_cyclic_upper_kernel<<<gl, 256, 0, h->stream>>>(tc, nt, (int)nt, g->d, tr ? g->y : g->x, tr ? g->x : g->y);
+        LAUNCH_CHECK(h);
+      } else {
+        CAP_TRY(copy2d(h, tc, nt, T, ldt, nt, nt, 4));
+      }
+      if (left) { L = tc; ldl = nt; } else { R = tc; ldr = nt; }
+      op.t_clean = true;
+    }
+    if (h->summa_pipeline == 1 || (h->summa_pipeline < 0 && g->num_chunks > 0)) return summa_pipelined(h, g, op, m, n, k, L, ldl, lr, lc, R, ldr, rr, rc, beta, C, ldc, S, lds, direct);
+    // serial panel loop (round 1): bcast -> bcast -> product, every collective on the compute stream
+    const int steps = d / c;
+    for (int s = 0; s < steps; ++s) {
+      const int kp = g->z + s * c;
+      const double *Lb, *Rb;
+      if (g->x == kp) { CAP_TRY(contiguous(h, CAP_WS_SUMMA_A, L, ldl, lr, lc, &Lb)); }
+      else { double* w; CAP_TRY(cap_workspace(h, CAP_WS_SUMMA_A, (size_t)lr * lc * sizeof(double), &w)); Lb = w; }
+      CAP_TRY(cap_bcast(h, g->row, const_cast<double*>(Lb), lr * lc, kp));
+      if (g->y == kp) { CAP_TRY(contiguous(h, CAP_WS_SUMMA_B, R, ldr, rr, rc, &Rb)); }
+      else { double* w; CAP_TRY(cap_workspace(h, CAP_WS_SUMMA_B, (size_t)rr * rc * sizeof(double), &w)); Rb = w; }
+      CAP_TRY(cap_bcast(h, g->column, const_cast<double*>(Rb), rr * rc, kp));
+      const int64_t ldlb = (Lb == L) ? ldl : lr, ldrb = (Rb == R) ? ldr : rr;
+      const double b = (s == 0) ? (direct ? beta : 0.0) : 1.0;
+      CAP_TRY(summa_local(h, op, m, n, k, 0, k, Lb, ldlb, Rb, ldrb, b, S, lds));
+    }
   }
   if (!direct) {
     if (c > 1) { CAP_TRY(cap_allreduce_sum(h, g->depth, S, m * n)); }       // collect (summa.hpp:236)

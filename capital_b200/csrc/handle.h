@@ -57,6 +57,8 @@ struct cap_handle_s {
   struct cap_comm_s* peer_failed_comm = nullptr;   // CUDA IPC mapping failed on this communicator: do not retry every call
   int lookahead_grid_mult = 64;       // tile-engine grid multiplier of the trailing update beside a chain (0 = keep the persistent grid)
   // chunked SUMMA (grid_algs.cuh): broadcasts / depth all-reduce on their own stream beside the local products
+  // pipelined panel loop: -1 = as the reference (only when the grid's num_chunks > 0, summa.hpp:177), 0 = never, 1 = always
+  int summa_pipeline = -1, summa_reserve_sms = 0, summa_halves = 1;
   cudaStream_t summa_stream = nullptr;
   cudaEvent_t ev_sready[2] = {}, ev_sfree[2] = {}, ev_shalf = nullptr, ev_sred[2] = {}, ev_sstart = nullptr;
   int lookahead_stair = 1;            // trailing update of the asynchronous schedule as ONE staircase launch (0 = a gemm + a syrk per run of blocks)

@@ -69,12 +69,6 @@ __global__ void assemble_row_panel_kernel(double* __restrict__ Rrow, const doubl
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n2; i += (int64_t)gridDim.x * blockDim.x) dst[i] = src[i];
 }
 
-struct SmCapScope {
-  cap_handle_t h; int saved;
-  SmCapScope(cap_handle_t h_, int cap) : h(h_), saved(h_->num_sms) { if (cap > 0 && cap < saved) h->num_sms = cap; }
-  ~SmCapScope() { h->num_sms = saved; }
-};
-
 struct GridMultScope {
   cap_handle_t h; int saved;
   GridMultScope(cap_handle_t h_, int mult) : h(h_), saved(h_->grid_mult) { if (mult > 0) h->grid_mult = mult; }
