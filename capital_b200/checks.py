@@ -239,6 +239,19 @@ def grid_small_check(eng, comm, world, rank, N=1024, verbose=False):
                 ok = ok and good
                 if verbose and rank == 0:
                     print("%-34s device %.3e numpy %.3e %s" % ("validate cholinv%s" % (" (damaged)" if damage else ""), got, ref, "ok" if good else "FAIL"), flush=True)
+    # the pipelined panel loop (num_chunks > 0, summa.hpp:177-215) on the same operands
+    gridp = cdist.Grid(eng, comm, c, 0, 3)
+    a, b, cm = loc(A), loc(B), loc(C0)
+    eng.summa_gemm(gridp, a, b, cm, l, l, l, "N", "N", 1.5, 0.5); torch.cuda.synchronize()
+    report("pipelined summa gemm NN", gather(cm), 1.5 * A @ B + 0.5 * C0)
+    t, b = loc(T), loc(B)
+    eng.summa_trmm(gridp, t, b, l, l, "R", "U", "N", "N", -1.0); torch.cuda.synchronize()
+    report("pipelined summa trmm R U N", gather(b), -B @ T)
+    s_loc, xinv = loc(S), colmajor(l, l)
+    eng.cholinv_factor(gridp, s_loc, xinv, True, 1, max(256, N // 4)); torch.cuda.synchronize()
+    report("pipelined cholinv R", gather(s_loc), np.linalg.cholesky(S).T)
+    report("pipelined cholinv Rinv", gather(xinv), np.linalg.inv(np.linalg.cholesky(S).T))
+    gridp.close()
     M = 8 * N
     Atall = rng.random((M, N))
     a_loc = loc(Atall); ml = M // d

@@ -116,11 +116,13 @@ def assemble_cyclic(blocks, d):
 class Grid:
     """topo::square over the library's NCCL communicator (cap_grid_t)."""
 
-    def __init__(self, engine, comm, c):
+    def __init__(self, engine, comm, c, layout=0, num_chunks=0):
+        """layout 0 / 1: the reference's two rank orders (only layout 0 matches grid_coords); num_chunks > 0 selects the
+        pipelined SUMMA panel loop (summa.hpp:177-215)."""
         from . import _lib
         self.lib = engine.lib
         self.ptr = C.c_void_p()
-        _lib.check(self.lib.cap_grid_create(comm.ptr if comm else None, int(c), C.byref(self.ptr)), "cap_grid_create")
+        _lib.check(self.lib.cap_grid_create2(comm.ptr if comm else None, int(c), int(layout), int(num_chunks), C.byref(self.ptr)), "cap_grid_create")
         v = [C.c_int() for _ in range(5)]
         self.lib.cap_grid_info(self.ptr, *[C.byref(t) for t in v])
         self.c, self.d, self.x, self.y, self.z = [t.value for t in v]
