@@ -160,6 +160,29 @@ def measure_fp64_peak(device_index):
     raise SystemExit("bench.py: no FP64 peak available (tools/dmma_peak failed: %s)" % err)
 
 
+def bind_to_gpu_numa_node(device_index):
+    """Pin this process to the CPUs of the NUMA node the GPU hangs off (sysfs), BEFORE the pinned host buffers of the
+    end-to-end leg are allocated: round 1 had all 8 ranks' buffers on node 0 and 107 GB/s aggregate over 8 PCIe links."""
+    try:
+        out = subprocess.run(["nvidia-smi", "--query-gpu=pci.bus_id", "--format=csv,noheader", "-i", str(device_index)],
+                             capture_output=True, text=True, timeout=20).stdout.strip()
+        bdf = out[-12:]                                          # 00000000:1B:00.0 -> 0000:1B:00.0
+        base = "/sys/bus/pci/devices/" + bdf.lower()
+        node = int(open(base + "/numa_node").read().strip())
+        cpus = open(base + "/local_cpulist").read().strip()
+        ids = set()
+        for part in cpus.split(","):
+            lo, _, hi = part.partition("-")
+            ids.update(range(int(lo), int(hi or lo) + 1))
+        allowed = ids & set(os.sched_getaffinity(0))
+        if node < 0 or not allowed:
+            return {"node": node, "bound": False}
+        os.sched_setaffinity(0, allowed)
+        return {"node": node, "cpus": len(allowed), "bound": True}
+    except Exception as exc:  # noqa: BLE001 -- binding is an optimisation, never a reason to lose the number
+        return {"bound": False, "error": str(exc)[:120]}
+
+
 def cpu_extra_baselines(cores):
     """cfg1 exactly through the reference's own bench main, and scaled cholinv / SUMMA runs of the
     unmodified reference (oracle/_ref).  Seconds are the reference's own MPI_Wtime bracket, max over its ranks."""
@@ -301,6 +324,7 @@ def ours_arm(args):
 
     # ---- end to end through the C ABI with HOST buffers (H2D + factor + D2H inside the timed region)
     e2e = None
+    numa = bind_to_gpu_numa_node(local_rank) if world > 1 else None      # pinned buffers are first-touched on the GPU's own node
     try:
         del A, Q
         torch.cuda.empty_cache()
@@ -320,7 +344,7 @@ def ours_arm(args):
         sec = cdist.max_over_ranks(time.perf_counter() - t0) / e2e_steps
         e2e = {"value": flops_cacqr2(m, n) / sec * 1e-12, "unit": "TFLOP/s", "h2d_bytes_per_step": m * n * 8,
                "d2h_bytes_per_step": m * n * 8 + world * n * n * 8, "ms_per_step": sec * 1e3, "steps": e2e_steps,
-               "h2d_plus_d2h_gbs_per_gpu": 2.0 * m_loc * n * 8 / sec * 1e-9,
+               "h2d_plus_d2h_gbs_per_gpu": 2.0 * m_loc * n * 8 / sec * 1e-9, "numa_binding": numa,
                "api": "cap_cacqr_factor_1d_host (pinned host A -> Q, R)"}
         del hA, hQ, hR
     except Exception as exc:  # noqa: BLE001 -- report, never fake, a missing end-to-end number
@@ -372,6 +396,32 @@ def ours_arm(args):
                     "lapack_info": eng.info(), "ok": eng.info() == 0}
         extra("config5", cfg5)
 
+    # ---- HBM-bound helpers of the path against the measured copy bandwidth of this pool's B200s
+    if world == 1 and not args.no_extras:
+        def helpers():
+            hbm = None
+            mp = os.path.join(ROOT, "MEASURED_PEAKS.json")
+            if os.path.exists(mp):
+                hbm = float(json.load(open(mp)).get("hbm_gbs", 0.0)) or None
+            nh = 16384
+            src = colmajor(nh, nh); dst = colmajor(nh, nh); src.uniform_()
+            packed = torch.empty(nh * (nh + 1) // 2, dtype=torch.float64, device="cuda")
+            full = 16.0 * nh * nh                                 # read + write of every element
+            rows = {}
+            def put(name, fn, nbytes):
+                ms = time_kernel(fn, 5)
+                rows[name] = {"ms": ms, "gbs": nbytes / ms * 1e-6, "frac_of_hbm_peak": (nbytes / ms * 1e-6 / hbm) if hbm else None}
+            put("copy2d mode 0 (all)", lambda: eng.copy2d(dst, src, nh, nh, 0), full)
+            put("copy2d mode 1 (upper only)", lambda: eng.copy2d(dst, src, nh, nh, 1), full / 2)
+            put("copy2d mode 3 (upper + zero lower)", lambda: eng.copy2d(dst, src, nh, nh, 3), 12.0 * nh * nh)
+            put("copy2d mode 0, strided view (ld 16384 -> 8192 rows)", lambda: eng.copy2d(dst[:8192], src[8192:], 8192, nh, 0), full / 2)
+            put("pack_upper", lambda: eng.pack_upper(packed, src, nh), full / 2)
+            put("unpack_upper + zero lower", lambda: eng.unpack_upper(dst, packed, nh, True), 12.0 * nh * nh)
+            put("axpby (y = a x + b y)", lambda: eng.axpby(dst, src, 0.5, 0.5), 24.0 * nh * nh)
+            return {"workload": "16384 x 16384 FP64 operands; algorithmic bytes / CUDA-event time, 5 launches each", "hbm_peak_gbs": hbm,
+                    "peak_source": "MEASURED_PEAKS.json hbm_gbs (driver-written)" if hbm else None, "kernels": rows, "ok": True}
+        extra("hbm_helpers", helpers)
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         try:
@@ -400,7 +450,7 @@ def ours_arm(args):
             "parity": parity, "parity_ok": bool(all_ok),
             "roofline": roofline, "cpu_baseline": cpu, "vs_cpu_baseline": (value / cpu["value"]) if cpu and cpu.get("value") else None,
             "lapack_info": info, "cholesky": extras.get("cholesky"), "cholinv_grid": extras.get("cholinv_grid"), "summa": extras.get("summa"),
-            "parity_small": extras.get("parity_small"), "config5": extras.get("config5"),
+            "parity_small": extras.get("parity_small"), "config5": extras.get("config5"), "hbm_helpers": extras.get("hbm_helpers"),
         }
         print(json.dumps(line), flush=True)
     eng.close()                 # the handle may own a duplicate of comm: it goes first

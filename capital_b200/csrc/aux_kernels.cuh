@@ -8,22 +8,65 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <algorithm>
+
 #include "potrf_leaf.cuh"
 
 namespace capk {
 
-// ---------------------------------------------------------------- HBM-bound helpers (vectorised where layout allows)
-// dst(r,c) = src(r,c) over an m x n window, column-major; mode: 0 all, 1 upper (r<=c) only, 2 lower only,
-// 3 upper copy + strict-lower zero, 4 lower copy + strict-upper zero.
-__global__ void copy2d_kernel(double* __restrict__ dst, int64_t ldd, const double* __restrict__ src, int64_t lds,
-                              int64_t m, int64_t n, int mode) {
-  const int64_t c = blockIdx.y;
-  for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < m; r += (int64_t)gridDim.x * blockDim.x) {
-    const bool up = r <= c, lo = r >= c;
-    if (mode == 0 || (mode == 1 && up) || (mode == 2 && lo)) dst[r + c * ldd] = src[r + c * lds];
-    else if (mode == 3) dst[r + c * ldd] = up ? src[r + c * lds] : 0.0;
-    else if (mode == 4) dst[r + c * ldd] = lo ? src[r + c * lds] : 0.0;
+// ---------------------------------------------------------------- HBM-bound helpers
+// dst(r,c) = src(r,c) over an m x n window, column-major; MODE: 0 all, 1 upper (r<=c) only, 2 lower only,
+// 3 upper copy + strict-lower zero, 4 lower copy + strict-upper zero.  VEC: both bases 16-byte aligned and both leading
+// dimensions even -- rows travel in pairs (one 16-byte access each way per thread and iteration).  Columns are walked with
+// a stride of gridDim.y, so any column count fits the 65535 limit of that grid dimension.
+template <int MODE, bool VEC>
+__global__ void copy2d_kernel(double* __restrict__ dst, int64_t ldd, const double* __restrict__ src, int64_t lds, int64_t m, int64_t n) {
+  auto keep = [](int64_t r, int64_t c) { return MODE == 0 || ((MODE == 1 || MODE == 3) ? r <= c : r >= c); };
+  for (int64_t c = blockIdx.y; c < n; c += gridDim.y) {
+    const double* s = src + c * lds;
+    double* d = dst + c * ldd;
+    if (VEC) {
+      const int64_t pairs = m >> 1;
+      for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < pairs; q += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = 2 * q;
+        const bool k0 = keep(r, c), k1 = keep(r + 1, c);
+        if (MODE == 1 || MODE == 2) {                     // masked entries of dst stay as they are
+          if (k0 && k1) *reinterpret_cast<double2*>(d + r) = *reinterpret_cast<const double2*>(s + r);
+          else { if (k0) d[r] = s[r]; if (k1) d[r + 1] = s[r + 1]; }
+        } else {
+          double2 v = make_double2(0.0, 0.0);
+          if (k0 || k1) v = *reinterpret_cast<const double2*>(s + r);
+          if (!k0) v.x = 0.0;
+          if (!k1) v.y = 0.0;
+          *reinterpret_cast<double2*>(d + r) = v;
+        }
+      }
+      if ((m & 1) && blockIdx.x == 0 && threadIdx.x == 0) {
+        const int64_t r = m - 1;
+        if (keep(r, c)) d[r] = s[r]; else if (MODE >= 3) d[r] = 0.0;
+      }
+    } else {
+      for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < m; r += (int64_t)gridDim.x * blockDim.x) {
+        if (keep(r, c)) d[r] = s[r]; else if (MODE >= 3) d[r] = 0.0;
+      }
+    }
   }
+}
+inline void launch_copy2d(cudaStream_t stream, double* dst, int64_t ldd, const double* src, int64_t lds, int64_t m, int64_t n, int mode) {
+  const bool vec = ((((uintptr_t)dst) | ((uintptr_t)src)) & 15) == 0 && ((ldd | lds) & 1) == 0 && m >= 2;
+  const int64_t work = vec ? (m + 1) / 2 : m;
+  const dim3 g((unsigned)std::min<int64_t>((work + 255) / 256, 4096), (unsigned)std::min<int64_t>(n, 65535));
+#define CAPK_COPY2D(M)                                                                            \
+  if (vec) copy2d_kernel<M, true><<<g, 256, 0, stream>>>(dst, ldd, src, lds, m, n);               \
+  else copy2d_kernel<M, false><<<g, 256, 0, stream>>>(dst, ldd, src, lds, m, n)
+  switch (mode) {
+    case 0: CAPK_COPY2D(0); break;
+    case 1: CAPK_COPY2D(1); break;
+    case 2: CAPK_COPY2D(2); break;
+    case 3: CAPK_COPY2D(3); break;
+    default: CAPK_COPY2D(4); break;
+  }
+#undef CAPK_COPY2D
 }
 
 // packed upper (reference uppertri offset X(X+1)/2+Y, src/matrix/structure.h:39) <-> full column-major

@@ -419,8 +419,7 @@ static int trmm_impl(cap_handle_t h, char side, char uplo, char trans, char diag
   if (!t_clean || unit) {  // masked copy of the referenced triangle (serialize-style), other half zero
     double* tc;
     CAP_TRY(cap_workspace(h, CAP_WS_TRI, (size_t)nt * nt * sizeof(double), &tc));
-    dim3 g((unsigned)((nt + 255) / 256), (unsigned)nt);
-    copy2d_kernel<<<g, 256, 0, h->stream>>>(tc, nt, T, ldt, nt, nt, upper ? 3 : 4);
+    launch_copy2d(h->stream, tc, nt, T, ldt, nt, nt, upper ? 3 : 4);
     LAUNCH_CHECK(h);
     if (unit) { set_unit_diag_kernel<<<(unsigned)((nt + 255) / 256), 256, 0, h->stream>>>(tc, nt, (int)nt); LAUNCH_CHECK(h); }
     T = tc; ldt = nt;
@@ -451,8 +450,7 @@ int cap_dtrmm(cap_handle_t h, char side, char uplo, char trans, char diag, int64
   if (m <= 0 || n <= 0) return CAP_OK;
   double* copy;  // left side: every output row block needs all of B's rows -> go through a copy of B
   CAP_TRY(cap_workspace(h, CAP_WS_PANEL, (size_t)m * n * sizeof(double), &copy));
-  dim3 g((unsigned)std::min<int64_t>((m + 255) / 256, 65535), (unsigned)n);
-  copy2d_kernel<<<g, 256, 0, h->stream>>>(copy, m, B, ldb, m, n, 0);
+  launch_copy2d(h->stream, copy, m, B, ldb, m, n, 0);
   LAUNCH_CHECK(h);
   return trmm_impl(h, side, uplo, trans, diag, m, n, alpha, T, ldt, copy, m, B, ldb, false, false);
 }
@@ -475,8 +473,8 @@ static int memset2d(cap_handle_t h, double* p, int64_t ld, int64_t m, int64_t n)
 }
 static int copy2d(cap_handle_t h, double* dst, int64_t ldd, const double* src, int64_t lds, int64_t m, int64_t n, int mode) {
   if (m <= 0 || n <= 0) return CAP_OK;
-  dim3 g((unsigned)std::min<int64_t>((m + 255) / 256, 65535), (unsigned)n);
-  copy2d_kernel<<<g, 256, 0, h->stream>>>(dst, ldd, src, lds, m, n, mode);
+  if (mode < 0 || mode > 4) return cap_fail(CAP_ERR_ARG, "cap_copy2d", "mode must be 0..4");
+  launch_copy2d(h->stream, dst, ldd, src, lds, m, n, mode);
   LAUNCH_CHECK(h);
   return CAP_OK;
 }
