@@ -19,35 +19,50 @@ namespace capk {
 // 3 upper copy + strict-lower zero, 4 lower copy + strict-upper zero.  VEC: both bases 16-byte aligned and both leading
 // dimensions even -- rows travel in pairs (one 16-byte access each way per thread and iteration).  Columns are walked with
 // a stride of gridDim.y, so any column count fits the 65535 limit of that grid dimension.
+constexpr int COPY_COLS = 8;      // columns per thread and pass: eight independent 16-byte loads in flight before the first store
 template <int MODE, bool VEC>
 __global__ void copy2d_kernel(double* __restrict__ dst, int64_t ldd, const double* __restrict__ src, int64_t lds, int64_t m, int64_t n) {
   auto keep = [](int64_t r, int64_t c) { return MODE == 0 || ((MODE == 1 || MODE == 3) ? r <= c : r >= c); };
-  for (int64_t c = blockIdx.y; c < n; c += gridDim.y) {
-    const double* s = src + c * lds;
-    double* d = dst + c * ldd;
+  for (int64_t c0 = (int64_t)blockIdx.y * COPY_COLS; c0 < n; c0 += (int64_t)gridDim.y * COPY_COLS) {
     if (VEC) {
       const int64_t pairs = m >> 1;
       for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < pairs; q += (int64_t)gridDim.x * blockDim.x) {
         const int64_t r = 2 * q;
-        const bool k0 = keep(r, c), k1 = keep(r + 1, c);
-        if (MODE == 1 || MODE == 2) {                     // masked entries of dst stay as they are
-          if (k0 && k1) *reinterpret_cast<double2*>(d + r) = *reinterpret_cast<const double2*>(s + r);
-          else { if (k0) d[r] = s[r]; if (k1) d[r + 1] = s[r + 1]; }
-        } else {
-          double2 v = make_double2(0.0, 0.0);
-          if (k0 || k1) v = *reinterpret_cast<const double2*>(s + r);
-          if (!k0) v.x = 0.0;
-          if (!k1) v.y = 0.0;
-          *reinterpret_cast<double2*>(d + r) = v;
+        double2 v[COPY_COLS];
+#pragma unroll
+        for (int j = 0; j < COPY_COLS; ++j) {
+          const int64_t c = c0 + j;
+          v[j] = make_double2(0.0, 0.0);
+          if (c < n && (keep(r, c) || keep(r + 1, c))) v[j] = *reinterpret_cast<const double2*>(src + c * lds + r);
+        }
+#pragma unroll
+        for (int j = 0; j < COPY_COLS; ++j) {
+          const int64_t c = c0 + j;
+          if (c >= n) continue;
+          double* d = dst + c * ldd + r;
+          const bool k0 = keep(r, c), k1 = keep(r + 1, c);
+          if (MODE == 1 || MODE == 2) {                   // masked entries of dst stay as they are
+            if (k0 && k1) *reinterpret_cast<double2*>(d) = v[j];
+            else { if (k0) d[0] = v[j].x; if (k1) d[1] = v[j].y; }
+          } else {
+            if (!k0) v[j].x = 0.0;
+            if (!k1) v[j].y = 0.0;
+            *reinterpret_cast<double2*>(d) = v[j];
+          }
         }
       }
-      if ((m & 1) && blockIdx.x == 0 && threadIdx.x == 0) {
-        const int64_t r = m - 1;
-        if (keep(r, c)) d[r] = s[r]; else if (MODE >= 3) d[r] = 0.0;
+      if ((m & 1) && blockIdx.x == 0 && threadIdx.x < COPY_COLS && c0 + threadIdx.x < n) {
+        const int64_t r = m - 1, c = c0 + threadIdx.x;
+        if (keep(r, c)) dst[c * ldd + r] = src[c * lds + r]; else if (MODE >= 3) dst[c * ldd + r] = 0.0;
       }
     } else {
       for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < m; r += (int64_t)gridDim.x * blockDim.x) {
-        if (keep(r, c)) d[r] = s[r]; else if (MODE >= 3) d[r] = 0.0;
+#pragma unroll
+        for (int j = 0; j < COPY_COLS; ++j) {
+          const int64_t c = c0 + j;
+          if (c >= n) continue;
+          if (keep(r, c)) dst[c * ldd + r] = src[c * lds + r]; else if (MODE >= 3) dst[c * ldd + r] = 0.0;
+        }
       }
     }
   }
@@ -55,7 +70,7 @@ __global__ void copy2d_kernel(double* __restrict__ dst, int64_t ldd, const doubl
 inline void launch_copy2d(cudaStream_t stream, double* dst, int64_t ldd, const double* src, int64_t lds, int64_t m, int64_t n, int mode) {
   const bool vec = ((((uintptr_t)dst) | ((uintptr_t)src)) & 15) == 0 && ((ldd | lds) & 1) == 0 && m >= 2;
   const int64_t work = vec ? (m + 1) / 2 : m;
-  const dim3 g((unsigned)std::min<int64_t>((work + 255) / 256, 4096), (unsigned)std::min<int64_t>(n, 65535));
+  const dim3 g((unsigned)std::min<int64_t>((work + 255) / 256, 4096), (unsigned)std::min<int64_t>((n + COPY_COLS - 1) / COPY_COLS, 65535));
 #define CAPK_COPY2D(M)                                                                            \
   if (vec) copy2d_kernel<M, true><<<g, 256, 0, stream>>>(dst, ldd, src, lds, m, n);               \
   else copy2d_kernel<M, false><<<g, 256, 0, stream>>>(dst, ldd, src, lds, m, n)
