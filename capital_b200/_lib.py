@@ -10,7 +10,7 @@ _i64, _int, _dbl, _ptr, _chr = C.c_int64, C.c_int, C.c_double, C.c_void_p, C.c_c
 
 _SIGS = {
     "cap_create": [C.POINTER(_ptr), _int], "cap_destroy": [_ptr], "cap_set_stream": [_ptr, _ptr],
-    "cap_synchronize": [_ptr], "cap_set_engine": [_ptr, _int], "cap_set_host_chunk_bytes": [_ptr, C.c_size_t], "cap_use_own_stream": [_ptr], "cap_release_workspace": [_ptr], "cap_set_peer_exchange": [_ptr, _int], "cap_set_update_grid": [_ptr, _int], "cap_get_info": [_ptr, C.POINTER(_int)], "cap_reset_info": [_ptr],
+    "cap_synchronize": [_ptr], "cap_set_engine": [_ptr, _int], "cap_set_host_chunk_bytes": [_ptr, C.c_size_t], "cap_use_own_stream": [_ptr], "cap_release_workspace": [_ptr], "cap_set_cacqr_complete_inv": [_ptr, _int], "cap_set_peer_exchange": [_ptr, _int], "cap_set_update_grid": [_ptr, _int], "cap_get_info": [_ptr, C.POINTER(_int)], "cap_reset_info": [_ptr],
     "cap_malloc": [C.POINTER(_ptr), C.c_size_t], "cap_free": [_ptr], "cap_memset_async": [_ptr, _ptr, _int, C.c_size_t],
     "cap_h2d_async": [_ptr, _ptr, _ptr, C.c_size_t], "cap_d2h_async": [_ptr, _ptr, _ptr, C.c_size_t],
     "cap_host_alloc": [C.POINTER(_ptr), C.c_size_t], "cap_host_free": [_ptr],

@@ -255,6 +255,19 @@ def grid_small_check(eng, comm, world, rank, N=1024, verbose=False):
     M = 8 * N
     Atall = rng.random((M, N))
     a_loc = loc(Atall); ml = M // d
+    # cacqr::solve (complete_inv = 0, cacqr.hpp:46-73): same Q and R through block back-substitution
+    eng.set_cacqr_complete_inv(False)
+    try:
+        q_loc, r_loc = colmajor(ml, l), colmajor(l, l)
+        eng.reset_info()
+        eng.cacqr_factor_3d(grid, a_loc, q_loc, r_loc, 2, None, 1, max(256, N // 4)); torch.cuda.synchronize()
+        Qr, Rr = np.linalg.qr(Atall)
+        sg = np.sign(np.diag(Rr)); Qr = Qr * sg; Rr = (Rr.T * sg).T
+        report("3D CQR2 R (solve, complete_inv=0)", gather(r_loc), Rr)
+        report("3D CQR2 Q (solve, complete_inv=0)", gather(q_loc), Qr)
+        ok = ok and eng.info() == 0
+    finally:
+        eng.set_cacqr_complete_inv(True)
     for iters in (1, 2):
         q_loc, r_loc = colmajor(ml, l), colmajor(l, l)
         eng.reset_info()

@@ -351,6 +351,10 @@ int cap_set_host_chunk_bytes(cap_handle_t h, size_t bytes) {
   return CAP_OK;
 }
 
+int cap_set_cacqr_complete_inv(cap_handle_t h, int complete_inv) {
+  h->cacqr_complete_inv = complete_inv ? 1 : 0;
+  return CAP_OK;
+}
 int cap_set_peer_exchange(cap_handle_t h, int mode) {
   if (mode < -1 || mode > 1) return cap_fail(CAP_ERR_ARG, "cap_set_peer_exchange", "-1 = peer copy engines when CUDA IPC works, 0 = NCCL only, 1 = peer copy engines required");
   h->peer_exchange = mode;

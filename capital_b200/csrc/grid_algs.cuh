@@ -575,8 +575,8 @@ int cap_cholinv_factor(cap_handle_t h, cap_grid_t g, int64_t n_loc, double* A, i
 // cacqr.hpp:86-98 is the c == d special case of the same contraction; here the grid-transposed copy of Q travels
 // along rows and Q along columns, so every c x d x d grid works), R = chol(G) and R^-1 by the distributed cholinv,
 // Q <- Q R^-1 by SUMMA-trmm (cacqr.hpp:104-108).  Two sweeps and R = R2 R1 (cacqr.hpp:203-211) for CholeskyQR2.
-// The block back-substitution variant (`solve`, cacqr.hpp:46-73, complete_inv == 0) produces the same Q; this entry
-// point always completes the inverse.
+// The block back-substitution variant (`solve`, cacqr.hpp:46-73, complete_inv == 0) produces the same Q without the
+// top-level inverse completion; selected by cap_set_cacqr_complete_inv(h, 0) (Rinv then lacks its top-level off-diagonal block).
 int cap_cacqr_factor_3d(cap_handle_t h, cap_grid_t g, int64_t m_loc, int64_t n_loc, const double* A, int64_t lda,
                         double* Q, int64_t ldq, double* R, int64_t ldr, double* Rinv, int64_t ldri,
                         int num_iter, int split, int64_t bc_global) {
@@ -594,8 +594,19 @@ int cap_cacqr_factor_3d(cap_handle_t h, cap_grid_t g, int64_t m_loc, int64_t n_l
     const int64_t ldg = it == 0 ? ldr : n_loc;
     CAP_TRY(memset2d(h, G, ldg, n_loc, n_loc));
     CAP_TRY(cap_summa_syrk(h, g, 'U', 'T', n_loc, m_loc, 1.0, Q, ldq, nullptr, 0, 0.0, G, ldg));
-    CAP_TRY(cap_cholinv_factor(h, g, n_loc, G, ldg, X, ldx, 1, split, bc_global));
-    CAP_TRY(cap_summa_trmm(h, g, 'R', 'U', 'N', 'N', m_loc, n_loc, 1.0, X, ldx, Q, ldq));
+    const int64_t s1 = n_loc >> split, s2 = n_loc - s1;
+    if (h->cacqr_complete_inv || s1 < 1 || s2 < 1) {
+      CAP_TRY(cap_cholinv_factor(h, g, n_loc, G, ldg, X, ldx, 1, split, bc_global));
+      CAP_TRY(cap_summa_trmm(h, g, 'R', 'U', 'N', 'N', m_loc, n_loc, 1.0, X, ldx, Q, ldq));
+    } else {
+      // cacqr::solve (cacqr.hpp:46-73): the inverse is left without its top-level off-diagonal block (cholinv.hpp:147) and
+      // Q = Q R^-1 is finished by block back-substitution:  Q1 <- Q1 Rinv11;  Q2 <- (Q2 - Q1 R12) Rinv22
+      CAP_TRY(cap_cholinv_factor(h, g, n_loc, G, ldg, X, ldx, 0, split, bc_global));
+      double* Q2 = Q + s1 * ldq;
+      CAP_TRY(summa_trmm_impl(h, g, 'R', 'U', 'N', 'N', m_loc, s1, 1.0, X, ldx, Q, ldq, true));
+      CAP_TRY(cap_summa_gemm(h, g, 'N', 'N', m_loc, s2, s1, -1.0, Q, ldq, G + s1 * ldg, ldg, 1.0, Q2, ldq));
+      CAP_TRY(summa_trmm_impl(h, g, 'R', 'U', 'N', 'N', m_loc, s2, 1.0, X + s1 + s1 * ldx, ldx, Q2, ldq, true));
+    }
   }
   if (num_iter == 2) {
     CAP_TRY(cap_summa_trmm(h, g, 'L', 'U', 'N', 'N', n_loc, n_loc, 1.0, R2, n_loc, R, ldr));   // R = R2 R1

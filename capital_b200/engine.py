@@ -107,6 +107,10 @@ class Engine:
     def set_lookahead(self, reserve_sms=16, pipeline=-1):
         _lib.check(self.lib.cap_set_lookahead(self.h, int(reserve_sms), int(pipeline)), "cap_set_lookahead")
 
+    def set_cacqr_complete_inv(self, complete_inv=True):
+        """3D CholeskyQR: True = completed inverse, False = cacqr::solve (cacqr.hpp:46-73)."""
+        _lib.check(self.lib.cap_set_cacqr_complete_inv(self.h, int(bool(complete_inv))), "cap_set_cacqr_complete_inv")
+
     def set_peer_exchange(self, mode=-1):
         """Panel exchange of potrf_1d: -1 = peer copy engines when CUDA IPC works, 0 = NCCL only, 1 = peer copy engines required."""
         _lib.check(self.lib.cap_set_peer_exchange(self.h, int(mode)), "cap_set_peer_exchange")

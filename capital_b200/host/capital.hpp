@@ -608,6 +608,7 @@ public:
     bc = bc < 1 ? 1 : bc; bc = bc > n ? n : bc;
     const int64_t bc_global = (int64_t)ci.d * (n / bc);
     capital::check(cap_reset_info(rt.handle()), "cap_reset_info");
+    capital::check(cap_set_cacqr_complete_inv(rt.handle(), ca.complete_inv ? 1 : 0), "cap_set_cacqr_complete_inv");   // 0: cacqr::solve (cacqr.hpp:46-73)
     capital::check(cap_cacqr_factor_3d(rt.handle(), ci.grid, m, n, A.data(), m, args.Q.data(), m, args.R.data(), n, nullptr, 0,
                                        (int)args.num_iter, (int)ca.split, bc_global), "cap_cacqr_factor_3d");
   }

@@ -205,6 +205,9 @@ int cap_cacqr_factor_1d_host(cap_handle_t h, cap_comm_t comm, int64_t m_loc, int
 int cap_cacqr_factor_3d(cap_handle_t h, cap_grid_t grid, int64_t m_loc, int64_t n_loc, const double* A, int64_t lda,
                         double* Q, int64_t ldq, double* R, int64_t ldr, double* Rinv, int64_t ldri,
                         int num_iter, int split, int64_t bc_global);
+/* complete_inv of the CholeskyQR's cholinv argument pack (cacqr.hpp:104-110): 1 (default) = Q <- Q Rinv with the completed
+ * inverse, 0 = cacqr::solve, block back-substitution with the inverse left without its top-level off-diagonal block */
+int cap_set_cacqr_complete_inv(cap_handle_t h, int complete_inv);
 
 /* ---- validators: the caller side of the path, on the device (test/qr/validate.hpp, test/cholesky/validate.hpp) ----
  * util::residual_local (src/util/util.hpp:27-53) as begin / accumulate / finish: accumulate adds sum w (X - Ref)^2 and
