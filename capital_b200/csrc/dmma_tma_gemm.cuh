@@ -392,8 +392,8 @@ __device__ __forceinline__ void store_tile(const TmaGemmParams& p, const TileInf
   const bool full = (m0 + BM <= p.M) && (n0 + BN <= p.N) && !ti.tri_diag;
   // C and Cin may be the same array, so the compiler has to keep every load of Cin in front of the store that follows it:
   // written element by element, beta != 0 costs 64 (32 paired) dependent round trips to L2 per thread -- 32 us per tile,
-  // measured (profiles/r02_update_probe.txt: time = K x ideal + 0.9 ms per 4096-tile launch at every K).  Hence batches
-  // (8 elements; larger ones spill): all reads of a batch are in flight before its first write.
+  // measured (profiles/r02_update_probe.txt: time = K x ideal + 0.9 ms per 4096-tile launch at every K).  Hence batches:
+  // all reads of a batch are in flight before its first write.
   if (!A_KC && p.c_vec2 && full) {
     // row tiles 2j and 2j+1 hold rows 16j+2g and 16j+2g+1: one 16-byte store per pair
 #pragma unroll
@@ -422,29 +422,37 @@ __device__ __forceinline__ void store_tile(const TmaGemmParams& p, const TileInf
     }
     return;
   }
+  constexpr int RB = 2;                      // row tiles per batch: 32 reads in flight (the accumulators hold 128 of the 240 registers)
 #pragma unroll
-  for (int i = 0; i < 8; ++i) {
-    const int r = m0 + acc_row<A_KC>(wm, i, g);
-    double o[4][2];
-    uint32_t live = 0;                       // bit (jj*2 + e): the element exists and is stored
+  for (int i0 = 0; i0 < 8; i0 += RB) {
+    double o[RB][4][2];
+    uint32_t live = 0;                       // bit (ii*8 + jj*2 + e): the element exists and is stored
 #pragma unroll
-    for (int jj = 0; jj < 4; ++jj)
+    for (int ii = 0; ii < RB; ++ii) {
+      const int r = m0 + acc_row<A_KC>(wm, i0 + ii, g);
 #pragma unroll
-      for (int e = 0; e < 2; ++e) {
-        const int c = n0 + acc_col<B_KC>(wn, jj, 2 * t + e);
-        bool ok = (r < p.M) && (c < p.N);
-        if (ti.tri_diag && p.c_tri == CTRI_UPPER && r - m0 > c - n0) ok = false;     // (a triangular C crosses a tile only where
-        if (ti.tri_diag && p.c_tri == CTRI_LOWER && r - m0 < c - n0) ok = false;     //  its row and column origins coincide)
-        live |= (ok ? 1u : 0u) << (jj * 2 + e);
-        o[jj][e] = (ok && beta != 0.0) ? p.Cin[r + (int64_t)c * p.ldcin] : 0.0;
-      }
+      for (int jj = 0; jj < 4; ++jj)
 #pragma unroll
-    for (int jj = 0; jj < 4; ++jj)
+        for (int e = 0; e < 2; ++e) {
+          const int c = n0 + acc_col<B_KC>(wn, jj, 2 * t + e);
+          bool ok = (r < p.M) && (c < p.N);
+          if (ti.tri_diag && p.c_tri == CTRI_UPPER && r - m0 > c - n0) ok = false;     // (a triangular C crosses a tile only where
+          if (ti.tri_diag && p.c_tri == CTRI_LOWER && r - m0 < c - n0) ok = false;     //  its row and column origins coincide)
+          live |= (ok ? 1u : 0u) << (ii * 8 + jj * 2 + e);
+          o[ii][jj][e] = (ok && beta != 0.0) ? p.Cin[r + (int64_t)c * p.ldcin] : 0.0;
+        }
+    }
 #pragma unroll
-      for (int e = 0; e < 2; ++e) {
-        const int c = n0 + acc_col<B_KC>(wn, jj, 2 * t + e);
-        if ((live >> (jj * 2 + e)) & 1u) C[r + (int64_t)c * p.ldc] = fma(beta, o[jj][e], alpha * acc[i][jj][e]);
-      }
+    for (int ii = 0; ii < RB; ++ii) {
+      const int r = m0 + acc_row<A_KC>(wm, i0 + ii, g);
+#pragma unroll
+      for (int jj = 0; jj < 4; ++jj)
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          const int c = n0 + acc_col<B_KC>(wn, jj, 2 * t + e);
+          if ((live >> (ii * 8 + jj * 2 + e)) & 1u) C[r + (int64_t)c * p.ldc] = fma(beta, o[ii][jj][e], alpha * acc[i0 + ii][jj][e]);
+        }
+    }
   }
 }
 
