@@ -25,7 +25,7 @@ _SIGS = {
     "cap_potrf_1d_block": [_i64, _int, C.POINTER(_int), C.POINTER(_int)],
     "cap_dpotrf": [_ptr, _chr, _int, _ptr, _int], "cap_dtrtri": [_ptr, _chr, _chr, _int, _ptr, _int],
     "cap_dcholinv": [_ptr, _int, _ptr, _i64, _ptr, _i64, _int],
-    "cap_cqr_gram": [_ptr, _i64, _i64, _ptr, _i64, _ptr, _i64],
+    "cap_cqr_gram": [_ptr, _i64, _i64, _ptr, _i64, _ptr, _i64], "cap_cqr_gram_noalloc": [_ptr, _i64, _i64, _ptr, _i64, _ptr, _i64],
     "cap_cqr_apply": [_ptr, _i64, _i64, _ptr, _i64, _ptr, _i64, _ptr, _i64],
     "cap_copy2d": [_ptr, _ptr, _i64, _ptr, _i64, _i64, _i64, _int],
     "cap_pack_upper": [_ptr, _ptr, _ptr, _i64, _int], "cap_unpack_upper": [_ptr, _ptr, _i64, _ptr, _int, _int],

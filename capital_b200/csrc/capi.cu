@@ -38,6 +38,8 @@ int cap_fail(int code, const char* what, const char* detail) {
     if (e_ != cudaSuccess) return cap_fail(CAP_ERR_CUDA, "kernel launch", cudaGetErrorString(e_)); \
   } while (0)
 
+static int noalloc_setup(cap_handle_s* h);   // defined with cap_cqr_gram_noalloc at the end of this file
+
 // ------------------------------------------------------------------------------------------ context
 int cap_create(cap_handle_t* out, int device) {
   int count = 0;
@@ -91,6 +93,7 @@ int cap_create(cap_handle_t* out, int device) {
     }
     h->encode_tiled = fn;
   }
+  CAP_TRY(noalloc_setup(h));     // address of the static scratch of cap_cqr_gram_noalloc on this device (no allocation)
   *out = h;
   return CAP_OK;
 }
@@ -933,4 +936,77 @@ struct SmCapScope {
 
 int cap_axpby2d(cap_handle_t h, double* y, int64_t ldy, const double* x, int64_t ldx, int64_t m, int64_t n, double alpha, double beta) {
   return axpby2d(h, y, ldy, x, ldx, m, n, alpha, beta, CTRI_FULL);
+}
+
+// ------------------------------------------------------------------------------------------ allocation-free entry point
+// cap_cqr_gram_noalloc: G(upper) = Q^T Q like cap_cqr_gram, for callers that cannot call cudaMalloc (CUDA graph capture,
+// tight serving loops, harnesses that forbid it).  No counterpart in the reference.
+// The split-K partials that cap_cqr_gram keeps in the handle's grown-on-demand workspace live here in a
+// file-scope device array of NOALLOC_SCRATCH_BYTES (32 MiB; every GPU that loads the library holds it until exit), so the
+// call makes no cudaMalloc / cudaFree and calls no allocating routine.  Limits: n <= CAP_GRAM_NOALLOC_MAX_N (512).
+// The array is shared by every call on the device and keeps the last call's contents: nothing in it has to start at zero
+// (every partial element the reduction reads is written by the product launch of the same call), but two calls that
+// overlap on the GPU (different streams or handles of one device) race on it.
+constexpr size_t NOALLOC_SCRATCH_BYTES = (size_t)32 << 20;
+constexpr size_t NOALLOC_SCRATCH_DOUBLES = NOALLOC_SCRATCH_BYTES / sizeof(double);
+static __device__ __align__(256) double g_noalloc_scratch[NOALLOC_SCRATCH_DOUBLES];
+
+// In host code `g_noalloc_scratch` is only a host-side stand-in for the symbol: its DEVICE address comes from
+// cudaGetSymbolAddress, once per device, with that device current (cap_create has just made it current).
+static double* g_noalloc_dev_ptr[64] = {};
+static int noalloc_setup(cap_handle_s* h) {
+  if (h->device < 0 || h->device >= 64) return cap_fail(CAP_ERR_ARG, "cap_create", "device index beyond 63");
+  if (!g_noalloc_dev_ptr[h->device]) {
+    double* ptr = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress((void**)&ptr, g_noalloc_scratch);
+    if (e != cudaSuccess || !ptr) { cudaGetLastError(); return cap_fail(CAP_ERR_CUDA, "cudaGetSymbolAddress(g_noalloc_scratch)", cudaGetErrorString(e)); }
+    g_noalloc_dev_ptr[h->device] = ptr;
+  }
+  h->noalloc_scratch = g_noalloc_dev_ptr[h->device];
+  return CAP_OK;
+}
+
+int cap_cqr_gram_noalloc(cap_handle_t h, int64_t m, int64_t n, const double* Q, int64_t ldq, double* G, int64_t ldg) {
+  if (m < 0 || n < 0 || m > INT32_MAX) return cap_fail(CAP_ERR_ARG, "cap_cqr_gram_noalloc", "bad dimension");
+  if (n > CAP_GRAM_NOALLOC_MAX_N)
+    return cap_fail(CAP_ERR_ARG, "cap_cqr_gram_noalloc", "n exceeds CAP_GRAM_NOALLOC_MAX_N (512): the static scratch holds no more; use cap_cqr_gram");
+  if (ldq < std::max<int64_t>(1, m) || ldg < std::max<int64_t>(1, n)) return cap_fail(CAP_ERR_ARG, "cap_cqr_gram_noalloc", "leading dimension too small");
+  if (!h->noalloc_scratch) return cap_fail(CAP_ERR_CUDA, "cap_cqr_gram_noalloc", "static scratch address was not resolved at cap_create");
+  if (n == 0) return CAP_OK;
+  GemmParams p{};
+  p.A = Q; p.B = Q; p.lda = ldq; p.ldb = ldq; p.C = G; p.Cin = G; p.ldc = ldg; p.ldcin = ldg;
+  p.M = (int)n; p.N = (int)n; p.K = (int)m; p.alpha = 1.0; p.beta = 0.0; p.c_tri = CTRI_UPPER;
+  p.tiles_m = p.tiles_n = (int)((n + BM - 1) / BM);
+  const int ntiles = p.tiles_m * (p.tiles_m + 1) / 2;
+  // k-slabs: about two work units per SM, slabs of at least 256 rows, and no more partials than the scratch holds
+  int64_t ksplit = std::min<int64_t>({(int64_t)(2 * h->num_sms) / ntiles, m / 256, (int64_t)(NOALLOC_SCRATCH_DOUBLES / (size_t)(n * n))});
+  ksplit = std::max<int64_t>(1, ksplit);
+  if (ksplit > 1) {
+    int kper = (int)((m + ksplit - 1) / ksplit);
+    kper = ((kper + BK - 1) / BK) * BK;
+    ksplit = (m + kper - 1) / kper;
+    if (ksplit > 1) { p.k_per_split = kper; p.c_split_stride = n * n; p.C = h->noalloc_scratch; p.ldc = n; }
+  }
+  p.ksplit = (int)ksplit;
+  if (tma_eligible(h, p)) {
+    CUtensorMap ma, mb;
+    CAP_TRY(make_map(h, &ma, p.A, p.K, p.M, p.lda, true));
+    CAP_TRY(make_map(h, &mb, p.B, p.K, p.N, p.ldb, true));
+    TmaGemmParams tp{};
+    tp.C = p.C; tp.Cin = p.Cin; tp.ldc = p.ldc; tp.ldcin = p.ldcin; tp.M = p.M; tp.N = p.N; tp.K = p.K;
+    tp.alpha = 1.0; tp.beta = 0.0; tp.c_tri = CTRI_UPPER; tp.diag = DIAG_NONE;
+    tp.ksplit = p.ksplit; tp.k_per_split = p.k_per_split; tp.c_split_stride = p.c_split_stride;
+    tp.tiles_m = p.tiles_m; tp.tiles_n = p.tiles_n; tp.sched = SCHED_TRI; tp.subs = 1; tp.units = ntiles * p.ksplit;
+    tp.c_vec2 = aligned16(tp.C, tp.ldc) ? 1 : 0;
+    launch_tma_t<true, true>(h, ma, mb, tp, std::min(tp.units, h->num_sms));
+  } else {
+    launch_gemm_t<true, false>(h, p, 1, dim3(ntiles, p.ksplit));
+  }
+  LAUNCH_CHECK(h);
+  if (p.ksplit > 1) {
+    splitk_reduce_kernel<<<dim3((unsigned)((n + 127) / 128), (unsigned)n), 128, 0, h->stream>>>(h->noalloc_scratch, p.c_split_stride, (int)n, p.ksplit, G, ldg,
+                                                                                            (int)n, (int)n, 1.0, 0.0, CTRI_UPPER);
+    LAUNCH_CHECK(h);
+  }
+  return CAP_OK;
 }

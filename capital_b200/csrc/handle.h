@@ -62,6 +62,7 @@ struct cap_handle_s {
   cudaStream_t summa_stream = nullptr;
   cudaEvent_t ev_sready[2] = {}, ev_sfree[2] = {}, ev_shalf = nullptr, ev_sred[2] = {}, ev_sstart = nullptr;
   int cacqr_complete_inv = 1;         // 3D CholeskyQR: 1 = Q <- Q Rinv with the completed inverse, 0 = cacqr::solve (block back-substitution)
+  double* noalloc_scratch = nullptr;  // device address of the static scratch of cap_cqr_gram_noalloc (cudaGetSymbolAddress at cap_create)
   int lookahead_stair = 1;            // trailing update of the asynchronous schedule as ONE staircase launch (0 = a gemm + a syrk per run of blocks)
   int grid_mult = 1;                  // tile engine: CTAs per SM worth of grid (1 = persistent, one CTA per SM)
   int ws_bank = 0;                    // which split-K workspace slot gemm launches use (1 while launching on the panel stream)

@@ -92,6 +92,13 @@ int cap_dcholinv(cap_handle_t h, int n, double* A, int64_t lda, double* Rinv, in
 /* ---- CholeskyQR fast paths (cacqr.hpp:7-29) -------------------------------------------------- */
 /* G(upper, n x n, ldg) <- Q^T Q for the local m x n row block; deterministic split-K. */
 int cap_cqr_gram(cap_handle_t h, int64_t m, int64_t n, const double* Q, int64_t ldq, double* G, int64_t ldg);
+/* Same result as cap_cqr_gram (upper triangle of G <- Q^T Q; summation order of the k-slabs may differ) WITHOUT any
+ * allocation: the split-K partials live in a 32 MiB file-scope device array instead of the handle's workspace, so the
+ * call is usable under CUDA graph capture or wherever cudaMalloc is forbidden.  No counterpart in the reference.
+ * Limit: n <= CAP_GRAM_NOALLOC_MAX_N, larger n returns CAP_ERR_ARG (any m).
+ * Every call on a device shares that array: calls that overlap on the GPU (two streams or handles of one device) race. */
+#define CAP_GRAM_NOALLOC_MAX_N 512
+int cap_cqr_gram_noalloc(cap_handle_t h, int64_t m, int64_t n, const double* Q, int64_t ldq, double* G, int64_t ldg);
 /* Qout <- Qin * triu(Rinv); Qout may equal Qin (in place) or be a different buffer. */
 int cap_cqr_apply(cap_handle_t h, int64_t m, int64_t n, const double* Rinv, int64_t ldr,
                   const double* Qin, int64_t ldqin, double* Qout, int64_t ldqout);
