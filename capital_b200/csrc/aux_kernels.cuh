@@ -85,16 +85,30 @@ inline void launch_copy2d(cudaStream_t stream, double* dst, int64_t ldd, const d
 }
 
 // packed upper (reference uppertri offset X(X+1)/2+Y, src/matrix/structure.h:39) <-> full column-major
+// (PACK_COLS columns per thread and pass: that many independent loads are in flight before the first store)
+constexpr int PACK_COLS = 8;
 __global__ void pack_upper_kernel(double* __restrict__ packed, const double* __restrict__ full, int64_t ld, int n) {
-  const int c = blockIdx.y;
-  for (int r = blockIdx.x * blockDim.x + threadIdx.x; r <= c && r < n; r += gridDim.x * blockDim.x)
-    packed[(int64_t)c * (c + 1) / 2 + r] = full[r + (int64_t)c * ld];
+  for (int c0 = blockIdx.y * PACK_COLS; c0 < n; c0 += gridDim.y * PACK_COLS) {
+    const int cmax = min(n, c0 + PACK_COLS) - 1;                     // last column of this group: rows beyond it belong to nobody
+    for (int r = blockIdx.x * blockDim.x + threadIdx.x; r <= cmax; r += gridDim.x * blockDim.x) {
+      double v[PACK_COLS];
+#pragma unroll
+      for (int j = 0; j < PACK_COLS; ++j) { const int c = c0 + j; v[j] = (c < n && r <= c) ? full[r + (int64_t)c * ld] : 0.0; }
+#pragma unroll
+      for (int j = 0; j < PACK_COLS; ++j) { const int c = c0 + j; if (c < n && r <= c) packed[(int64_t)c * (c + 1) / 2 + r] = v[j]; }
+    }
+  }
 }
 __global__ void unpack_upper_kernel(double* __restrict__ full, int64_t ld, const double* __restrict__ packed, int n, int zero_lower) {
-  const int c = blockIdx.y;
-  for (int r = blockIdx.x * blockDim.x + threadIdx.x; r < n; r += gridDim.x * blockDim.x) {
-    if (r <= c) full[r + (int64_t)c * ld] = packed[(int64_t)c * (c + 1) / 2 + r];
-    else if (zero_lower) full[r + (int64_t)c * ld] = 0.0;
+  for (int c0 = blockIdx.y * PACK_COLS; c0 < n; c0 += gridDim.y * PACK_COLS) {
+    const int rmax = zero_lower ? n - 1 : min(n, c0 + PACK_COLS) - 1;
+    for (int r = blockIdx.x * blockDim.x + threadIdx.x; r <= rmax; r += gridDim.x * blockDim.x) {
+      double v[PACK_COLS];
+#pragma unroll
+      for (int j = 0; j < PACK_COLS; ++j) { const int c = c0 + j; v[j] = (c < n && r <= c) ? packed[(int64_t)c * (c + 1) / 2 + r] : 0.0; }
+#pragma unroll
+      for (int j = 0; j < PACK_COLS; ++j) { const int c = c0 + j; if (c < n && (r <= c || zero_lower)) full[r + (int64_t)c * ld] = v[j]; }
+    }
   }
 }
 
@@ -139,7 +153,7 @@ __global__ void fill_random_kernel(double* __restrict__ dst, int64_t ld, int64_t
 // srand48(max + globalDimY*min); + diag_add where global row == global col and local row == local col.
 __global__ void fill_symmetric_kernel(double* __restrict__ dst, int64_t ld, int64_t rows, int64_t cols, int64_t px, int64_t py,
                                       int64_t grid_x, int64_t grid_y, int64_t global_y, double diag_add) {
-  const int64_t c = blockIdx.y;
+  for (int64_t c = blockIdx.y; c < cols; c += gridDim.y)
   for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < rows; r += (int64_t)gridDim.x * blockDim.x) {
     const int64_t gx = px + c * grid_x, gy = py + r * grid_y;
     const long long seed = gx > gy ? gx + global_y * gy : gy + global_y * gx;

@@ -304,7 +304,7 @@ static int gemm_launch(cap_handle_t h, GemmParams p, bool ta, bool tb, int want_
     LAUNCH_CHECK(h);
   }
   if (ksplit > 1) {
-    dim3 rg((p.M + 127) / 128, p.N);
+    dim3 rg((p.M + 127) / 128, std::min(p.N, 65535));
     splitk_reduce_kernel<<<rg, 128, 0, h->stream>>>(p.C, p.c_split_stride, p.M, ksplit, user_c, user_ldc, p.M, p.N, alpha, beta, p.c_tri);
     LAUNCH_CHECK(h);
   }
@@ -727,13 +727,13 @@ int cap_copy2d(cap_handle_t h, double* dst, int64_t ldd, const double* src, int6
 }
 int cap_pack_upper(cap_handle_t h, double* packed, const double* full, int64_t ld, int n) {
   if (n <= 0) return CAP_OK;
-  pack_upper_kernel<<<dim3((n + 255) / 256, n), 256, 0, h->stream>>>(packed, full, ld, n);
+  pack_upper_kernel<<<dim3((n + 255) / 256, std::min((n + PACK_COLS - 1) / PACK_COLS, 65535)), 256, 0, h->stream>>>(packed, full, ld, n);
   LAUNCH_CHECK(h);
   return CAP_OK;
 }
 int cap_unpack_upper(cap_handle_t h, double* full, int64_t ld, const double* packed, int n, int zero_lower) {
   if (n <= 0) return CAP_OK;
-  unpack_upper_kernel<<<dim3((n + 255) / 256, n), 256, 0, h->stream>>>(full, ld, packed, n, zero_lower);
+  unpack_upper_kernel<<<dim3((n + 255) / 256, std::min((n + PACK_COLS - 1) / PACK_COLS, 65535)), 256, 0, h->stream>>>(full, ld, packed, n, zero_lower);
   LAUNCH_CHECK(h);
   return CAP_OK;
 }
@@ -755,7 +755,7 @@ int cap_fill_random(cap_handle_t h, double* dst, int64_t ld, int64_t rows, int64
 int cap_fill_symmetric(cap_handle_t h, double* dst, int64_t ld, int64_t rows, int64_t cols, int64_t px, int64_t py,
                        int64_t grid_x, int64_t grid_y, int64_t global_dim, int diagonally_dominant) {
   if (rows <= 0 || cols <= 0) return CAP_OK;
-  dim3 g((unsigned)std::min<int64_t>((rows + 255) / 256, 65535), (unsigned)cols);
+  dim3 g((unsigned)std::min<int64_t>((rows + 255) / 256, 65535), (unsigned)std::min<int64_t>(cols, 65535));
   fill_symmetric_kernel<<<g, 256, 0, h->stream>>>(dst, ld, rows, cols, px, py, grid_x, grid_y, global_dim, diagonally_dominant ? (double)global_dim : 0.0);
   LAUNCH_CHECK(h);
   return CAP_OK;

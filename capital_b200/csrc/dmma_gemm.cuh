@@ -370,15 +370,17 @@ __global__ void __launch_bounds__(SMALL_THREADS) dmma_small_gemm_kernel(const Ge
 // Deterministic split-K reduction: C = alpha * sum_z part[z] + beta*C over one triangle or the full matrix.
 __global__ void splitk_reduce_kernel(const double* __restrict__ part, int64_t part_stride, int ld_part, int ksplit,
                                      double* C, int64_t ldc, int M, int N, double alpha, double beta, int c_tri) {
-  const int r = blockIdx.x * blockDim.x + threadIdx.x, c = blockIdx.y;
-  if (r >= M || c >= N) return;
-  if (c_tri == CTRI_UPPER && r > c) return;
-  if (c_tri == CTRI_LOWER && r < c) return;
-  double s = 0.0;
-  for (int z = 0; z < ksplit; ++z) s += part[(int64_t)z * part_stride + r + (int64_t)c * ld_part];
-  double v = alpha * s;
-  if (beta != 0.0) v += beta * C[r + (int64_t)c * ldc];
-  C[r + (int64_t)c * ldc] = v;
+  const int r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= M) return;
+  for (int c = blockIdx.y; c < N; c += gridDim.y) {      // (columns strided: any N fits the 65535 limit of gridDim.y)
+    if (c_tri == CTRI_UPPER && r > c) continue;
+    if (c_tri == CTRI_LOWER && r < c) continue;
+    double s = 0.0;
+    for (int z = 0; z < ksplit; ++z) s += part[(int64_t)z * part_stride + r + (int64_t)c * ld_part];
+    double v = alpha * s;
+    if (beta != 0.0) v += beta * C[r + (int64_t)c * ldc];
+    C[r + (int64_t)c * ldc] = v;
+  }
 }
 
 }  // namespace capk

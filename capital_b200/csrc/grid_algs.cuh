@@ -75,7 +75,7 @@ int cap_grid_transpose(cap_handle_t h, cap_grid_t g, const double* src, double* 
 
 __global__ void axpby2d_kernel(double* __restrict__ y, int64_t ldy, const double* __restrict__ x, int64_t ldx, int64_t m, int64_t n,
                                double alpha, double beta, int tri) {
-  const int64_t c = blockIdx.y;
+  for (int64_t c = blockIdx.y; c < n; c += gridDim.y)
   for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < m; r += (int64_t)gridDim.x * blockDim.x) {
     if (tri == CTRI_UPPER && r > c) continue;
     if (tri == CTRI_LOWER && r < c) continue;
@@ -85,7 +85,7 @@ __global__ void axpby2d_kernel(double* __restrict__ y, int64_t ldy, const double
 }
 static int axpby2d(cap_handle_t h, double* y, int64_t ldy, const double* x, int64_t ldx, int64_t m, int64_t n, double alpha, double beta, int tri) {
   if (m <= 0 || n <= 0) return CAP_OK;
-  dim3 gr((unsigned)std::min<int64_t>((m + 255) / 256, 65535), (unsigned)n);
+  dim3 gr((unsigned)std::min<int64_t>((m + 255) / 256, 65535), (unsigned)std::min<int64_t>(n, 65535));
   axpby2d_kernel<<<gr, 256, 0, h->stream>>>(y, ldy, x, ldx, m, n, alpha, beta, tri);
   LAUNCH_CHECK(h);
   return CAP_OK;
@@ -286,6 +286,9 @@ static int summa_core(cap_handle_t h, cap_grid_t g, SummaOp op, int64_t m, int64
   const bool in_place_hazard = (c == 1) && (C == L || C == R);   // trmm writes its own operand: go through the partial buffer
   if (in_place_hazard) { CAP_TRY(cap_workspace(h, CAP_WS_SUMMA_C, (size_t)m * n * sizeof(double), &S)); lds = m; }
   const bool direct = (S == C);
+  // a triangular product writes one triangle of the partial buffer only, and the depth all-reduce sums all of it: the other
+  // triangle must not carry whatever the workspace held (uninitialised, possibly NaN, data through the collective)
+  if (!direct && op.c_tri != CTRI_FULL) CAP_TRY(memset2d(h, S, lds, m, n));
   if (d == 1) {
     if (op.kind != SUMMA_GEMM && c > 1 && (!op.t_clean || is_u(op.diag))) {
       // k-slices of a triangular operand are multiplied as general panels: materialise the zero triangle once
@@ -313,7 +316,7 @@ static int summa_core(cap_handle_t h, cap_grid_t g, SummaOp op, int64_t m, int64
       CAP_TRY(cap_workspace(h, CAP_WS_SUMMA_T, (size_t)nt * nt * sizeof(double), &tc));
       if (is_u(op.uplo)) {
         CAP_TRY(copy2d(h, tc, nt, T, ldt, nt, nt, 0));
-        dim3 gl((unsigned)((nt + 255) / 256), (unsigned)nt);
+        dim3 gl((unsigned)((nt + 255) / 256), (unsigned)std::min<int64_t>(nt, 65535));
         // op(T) = T^T: the caller hands in the grid-transposed block (util::transpose, as cholinv.hpp:116-118 does), i.e. the
         // block of the process at (y, x)
         const bool tr = is_t(op.trans);
@@ -425,7 +428,7 @@ __global__ void cyclic_to_local_kernel(double* __restrict__ dst, int64_t ldd, co
 }
 
 __global__ void mask_cyclic_upper_kernel(double* __restrict__ A, int64_t lda, int len, int d, int x, int y) {
-  const int c = blockIdx.y;
+  for (int c = blockIdx.y; c < len; c += gridDim.y)
   for (int r = blockIdx.x * blockDim.x + threadIdx.x; r < len; r += gridDim.x * blockDim.x)
     if (y + (int64_t)d * r > x + (int64_t)d * c) A[r + (int64_t)c * lda] = 0.0;
 }
@@ -561,7 +564,7 @@ int cap_cholinv_factor(cap_handle_t h, cap_grid_t g, int64_t n_loc, double* A, i
     fprintf(stderr, "\n");
   }
   // the strictly-lower local part of A still holds input values: R is upper (remove_triangle, util.hpp:267-293)
-  dim3 gl((unsigned)((n_loc + 255) / 256), (unsigned)n_loc);
+  dim3 gl((unsigned)((n_loc + 255) / 256), (unsigned)std::min<int64_t>(n_loc, 65535));
   mask_cyclic_upper_kernel<<<gl, 256, 0, h->stream>>>(A, lda, (int)n_loc, g->d, g->x, g->y);
   LAUNCH_CHECK(h);
   return CAP_OK;
