@@ -811,7 +811,10 @@ int cap_cacqr_factor_1d_host(cap_handle_t h, cap_comm_t comm, int64_t m_loc, int
   double *G1 = ws, *G2 = ws + nn, *Rinv = ws + 2 * nn, *packed = ws + 3 * nn;
   if (!h->ev_a) { CUDA_TRY(cudaEventCreateWithFlags(&h->ev_a, cudaEventDisableTiming)); CUDA_TRY(cudaEventCreateWithFlags(&h->ev_b, cudaEventDisableTiming)); }
   // chunks of ~1 GiB, multiples of 128 rows (tile height), at most 32
-  int64_t rows_per = ((std::max<int64_t>(1, (int64_t)h->host_chunk_bytes / (n * 8)) + 127) / 128) * 128;
+  // (and at least 16 chunks when the block is large enough for chunks of >= 64 MiB: with few chunks per rank -- 4 at 8 GPUs in
+  //  round 1 -- the un-overlapped first upload and last download are a visible part of the step)
+  const int64_t chunk_bytes = std::min<int64_t>((int64_t)h->host_chunk_bytes, std::max<int64_t>((int64_t)64 << 20, (int64_t)bytes / 16));
+  int64_t rows_per = ((std::max<int64_t>(1, chunk_bytes / (n * 8)) + 127) / 128) * 128;
   if ((m_loc + rows_per - 1) / rows_per > 32) rows_per = (((m_loc + 31) / 32 + 127) / 128) * 128;
   const int nchunks = m_loc > 0 ? (int)((m_loc + rows_per - 1) / rows_per) : 0;
   cudaStream_t cs = h->copy_stream;
