@@ -379,7 +379,7 @@ def ours_arm(args):
         ps["ok"] = bool(ps["cacqr2_1d"]["ok"] and ps["potrf_1d"]["ok"] and ps["grid"]["ok"])
     def cholesky():
         # block width: the bulk update prefers wide panels, the diagonal chain narrow ones; both candidates are run and named
-        cands = [2048, 1024] if world <= 2 else [1024, 768]
+        cands = [2048, 1024] if world <= 2 else [1024, 512]
         runs = [checks.cholesky_block(eng, comm_ptr, world, rank, n_chol, nb, 3, peak) for nb in cands]
         best = min(runs, key=lambda r: r["ms"])
         best = dict(best, tried=[{"nb": r["nb"], "ms": r["ms"], "resid_sampled": r["resid_sampled"], "ok": r["ok"]} for r in runs])
