@@ -55,7 +55,7 @@ _SIGS = {
     "cap_validate_cholinv": [_ptr, _ptr, _i64, _ptr, _i64, _ptr, _i64, _ptr],
     "cap_cacqr_factor_3d": [_ptr, _ptr, _i64, _i64, _ptr, _i64, _ptr, _i64, _ptr, _i64, _ptr, _i64, _int, _int, _i64],
 }
-EXPORTS = sorted(list(_SIGS) + ["cap_last_error", "cap_get_stream", "cap_kernel_launches"])
+EXPORTS = sorted(list(_SIGS) + ["cap_last_error", "cap_get_stream", "cap_kernel_launches", "cap_debug_stair_decode"])
 
 _lib = None
 
@@ -80,6 +80,8 @@ def load():
     lib.cap_last_error.restype = C.c_char_p
     lib.cap_get_stream.argtypes, lib.cap_get_stream.restype = [_ptr], _ptr
     lib.cap_kernel_launches.argtypes, lib.cap_kernel_launches.restype = [_ptr], C.c_longlong
+    lib.cap_debug_stair_decode.argtypes = [_int, _int, _int, _int, _int, _int, _i64, C.POINTER(_int), C.POINTER(_int), C.POINTER(_int)]
+    lib.cap_debug_stair_decode.restype = _i64
     _lib = lib
     return lib
 

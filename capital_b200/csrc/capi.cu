@@ -348,6 +348,26 @@ static int stair_launch(cap_handle_t h, const double* A, int64_t lda, const doub
   return CAP_OK;
 }
 
+// Host-side view of the staircase enumeration (the very function the kernel decodes its work with), for CPU tests.
+// Returns the number of work units of the launch geometry; unit >= 0 also decodes that unit.
+int64_t cap_debug_stair_decode(int T, int P, int me, int r_first, int row0, int tiles_n, int64_t unit, int* tm, int* tn, int* tri) {
+  int64_t units = 0;
+  for (int bi = 0; bi * T < tiles_n; ++bi) {
+    const int rb = r_first + bi;
+    const int gblk = rb * P + ((rb & 1) ? P - 1 - me : me);
+    const int Tb = std::min(T, tiles_n - bi * T);
+    const int base = (gblk - row0) * T + 1;
+    if (base < 1) return -1;
+    units += (int64_t)Tb * base + (int64_t)Tb * (Tb - 1) / 2;
+  }
+  if (unit >= 0 && unit < units) {
+    int a = 0, b = 0; bool t = false;
+    capk::stair_decode(T, P, me, r_first, row0, tiles_n, (int)unit, a, b, t);
+    if (tm) *tm = a; if (tn) *tn = b; if (tri) *tri = t ? 1 : 0;
+  }
+  return units;
+}
+
 int cap_set_host_chunk_bytes(cap_handle_t h, size_t bytes) {
   if (bytes < 4096) return cap_fail(CAP_ERR_ARG, "cap_set_host_chunk_bytes", "chunk too small");
   h->host_chunk_bytes = bytes;

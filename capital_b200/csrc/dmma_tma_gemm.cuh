@@ -98,30 +98,34 @@ struct TileInfo { int tm, tn, kz, k_first, k_step, nk, diag_origin; bool tri_dia
 struct TrueTag { static constexpr bool value = true; };
 struct FalseTag { static constexpr bool value = false; };
 
+// SCHED_STAIR: column-major walk over the tiles of every block column that lie on or above the global diagonal.  The column
+// tile `ct` of local block rb (global block g under the boustrophedon deal) has (g - row0) * T + ct + 1 row tiles, the last of
+// which is triangular.  Host-callable: tests/test_potrf1d_host.py enumerates it on the CPU through cap_debug_stair_decode.
+__host__ __device__ inline void stair_decode(int T, int P, int me, int r_first, int row0, int tiles_n, int unit, int& tm, int& tn, bool& tri) {
+  int rem = unit;
+  for (int bi = 0;; ++bi) {
+    const int rb = r_first + bi;
+    const int g = rb * P + ((rb & 1) ? P - 1 - me : me);
+    const int Tb = (T < tiles_n - bi * T) ? T : tiles_n - bi * T;
+    const int base = (g - row0) * T + 1;
+    const int cnt = Tb * base + Tb * (Tb - 1) / 2;
+    if (rem < cnt || (bi + 1) * T >= tiles_n) {
+      int ct = 0;
+      while (ct + 1 < Tb && rem >= base + ct) { rem -= base + ct; ++ct; }
+      tn = bi * T + ct; tm = rem; tri = (rem == base + ct - 1);
+      return;
+    }
+    rem -= cnt;
+  }
+}
+
 __device__ __forceinline__ TileInfo decode_tile(const TmaGemmParams& p, int unit, int sub) {
   TileInfo t;
   int tile = unit;
   t.kz = 0;
   t.tri_diag = false;
   if (p.sched == SCHED_STAIR) {
-    // column-major walk over the tiles of every block column that lie on or above the global diagonal: the column tile
-    // `ct` of local block rb (global block g) has (g - row0) * T + ct + 1 row tiles, the last of which is triangular
-    const int T = p.stair_T;
-    int rem = unit;
-    for (int bi = 0;; ++bi) {
-      const int rb = p.stair_r_first + bi;
-      const int g = rb * p.stair_P + ((rb & 1) ? p.stair_P - 1 - p.stair_me : p.stair_me);
-      const int Tb = min(T, p.tiles_n - bi * T);
-      const int base = (g - p.stair_row0) * T + 1;
-      const int cnt = Tb * base + Tb * (Tb - 1) / 2;
-      if (rem < cnt || (bi + 1) * T >= p.tiles_n) {
-        int ct = 0;
-        while (ct + 1 < Tb && rem >= base + ct) { rem -= base + ct; ++ct; }
-        t.tn = bi * T + ct; t.tm = rem; t.tri_diag = (rem == base + ct - 1);
-        break;
-      }
-      rem -= cnt;
-    }
+    stair_decode(p.stair_T, p.stair_P, p.stair_me, p.stair_r_first, p.stair_row0, p.tiles_n, unit, t.tm, t.tn, t.tri_diag);
   } else
   if (p.sched == SCHED_ROWPANEL_DESC) { t.tm = unit; t.tn = p.tiles_n - 1 - sub; }
   else if (p.sched == SCHED_ROWPANEL_ASC) { t.tm = unit; t.tn = sub; }

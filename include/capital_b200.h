@@ -175,6 +175,10 @@ int cap_cholinv_factor(cap_handle_t h, cap_grid_t grid, int64_t n_loc, double* A
 int cap_potrf_1d(cap_handle_t h, cap_comm_t comm, int64_t N, int nb, double* A_loc, int64_t lda);
 int cap_potrf_1d_layout(int64_t N, int nb, int nranks, int rank, int64_t* ncols_loc, int* nblocks_loc);
 int cap_potrf_1d_block(int64_t j, int nranks, int* owner, int* local_block);
+/* test hook (host only, no device work): the tile enumeration of the one-launch trailing update of cap_potrf_1d.  Geometry:
+ * T = nb / 128 tiles per block, P ranks, this rank `me`, first local block r_first, first row block row0, tiles_n column
+ * tiles.  Returns the number of work units (-1: a block column left of row0); unit >= 0 also yields that unit's tile. */
+int64_t cap_debug_stair_decode(int T, int P, int me, int r_first, int row0, int tiles_n, int64_t unit, int* tm, int* tn, int* tri);
 /* reserve_sms: SMs the trailing update leaves to a diagonal-block chain running beside it (default 16; 0 = none).
  * pipeline: -1 (default) = the asynchronous schedule: the chain leaf -> X -> next diagonal block runs two panels ahead of
  * the trailing update on its owner, and between ranks every solved block is written into the peers' row-panel buffers by

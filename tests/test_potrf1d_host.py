@@ -264,3 +264,37 @@ def test_schedule_over_gloo_matches_lapack(tmp_path, world, n, nb, port):
             rows = (j + 1) * nb
             assert np.allclose(np.triu(got[:rows], -j * nb), np.triu(want[:rows], -j * nb), rtol=1e-11, atol=1e-12)
             assert np.array_equal(np.tril(got, -j * nb - 1), np.tril(a[:, j * nb:j * nb + L.width(j)], -j * nb - 1))
+
+
+@pytest.mark.parametrize("P,nb,nblk,ragged", [(1, 128, 9, 0), (1, 512, 7, 100), (2, 256, 11, 0), (3, 384, 10, 200), (4, 128, 17, 1), (8, 1024, 32, 0), (8, 256, 37, 129)])
+def test_staircase_enumeration_covers_the_trailing_update_exactly(P, nb, nblk, ragged):
+    """One launch = the whole trailing update of a rank (SCHED_STAIR, dmma_tma_gemm.cuh): the kernel's own tile decoder,
+    called on the host through cap_debug_stair_decode, must visit every 128 x 128 tile of the rank's block columns >= j+3 that
+    lies on or above the GLOBAL diagonal exactly once, rows counted from block row j+2, and flag exactly the diagonal tiles."""
+    lib = _lib.load()
+    T = nb // 128
+    N = nblk * nb - (nb - ragged if ragged else 0)
+    L = Layout(P, nb, N)
+    for j in range(0, max(1, L.nblk - 2), max(1, L.nblk // 5)):
+        for me in range(P):
+            mine = cdist.potrf_1d_blocks(N, nb, P, me)
+            r = next((i for i, g in enumerate(mine) if g >= j + 3), None)
+            if r is None:
+                continue
+            cols = sum(min(nb, N - g * nb) for g in mine[r:])
+            tiles_n = -(-cols // 128)
+            row0 = j + 2
+            want = {}
+            for bi, g in enumerate(mine[r:]):
+                for ct in range(-(-min(nb, N - g * nb) // 128)):
+                    for tm in range((g - row0) * T + ct + 1):
+                        want[(tm, bi * T + ct)] = (tm == (g - row0) * T + ct)
+            tm, tn, tri = C.c_int(), C.c_int(), C.c_int()
+            units = lib.cap_debug_stair_decode(T, P, me, r, row0, tiles_n, -1, None, None, None)
+            assert units == len(want), (j, me, units, len(want))
+            got = {}
+            for u in range(units):
+                lib.cap_debug_stair_decode(T, P, me, r, row0, tiles_n, u, C.byref(tm), C.byref(tn), C.byref(tri))
+                assert (tm.value, tn.value) not in got
+                got[(tm.value, tn.value)] = bool(tri.value)
+            assert got == want
