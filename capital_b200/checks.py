@@ -8,6 +8,8 @@ None of it imports oracle/ -- bench.py may only touch the oracle in its cpu_base
 Metrics follow the reference's validators: test/qr/validate.hpp:7-52 (orthogonality ||Q^T Q - I||_F / n,
 residual ||Q R - A||_F / ||A||_F) and test/cholesky/validate.hpp:7-48 (||R^T R - A||_F / ||A||_F).
 """
+import os
+
 import numpy as np
 import torch
 import torch.distributed as dist
@@ -268,6 +270,30 @@ def grid_small_check(eng, comm, world, rank, N=1024, verbose=False):
         ok = ok and eng.info() == 0
     finally:
         eng.set_cacqr_complete_inv(True)
+    # every rank's LOCAL blocks against the reference itself: tests/golden/cacqr3d.npz holds qr::cacqr::factor of the unmodified
+    # reference on the 2x2x2 cube (8 mini-MPI ranks); the d = 2 face of worlds 4 (1x2x2) and 8 (2x2x2) holds the same blocks
+    fixture = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden", "cacqr3d.npz")
+    if d == 2 and os.path.exists(fixture):
+        try:
+            fx = np.load(fixture)
+            for tag in ("ci1", "ci0"):
+                _, variant, m_f, n_f, c_f, d_f, ci = [int(v) for v in fx[tag + "_meta"]]
+                rf = c_f * (x + d_f * y)                                   # the fixture's rank at (x, y, z = 0)
+                a_f = colmajor(m_f // d_f, n_f // d_f); eng.fill_random(a_f, rf // c_f)   # bench/qr/cacqr.cpp:34: key = rank / c
+                same_input = bool(np.array_equal(a_f.cpu().numpy(), fx["%s_A_r%d" % (tag, rf)]))
+                q_f, r_f = colmajor(m_f // d_f, n_f // d_f), colmajor(n_f // d_f, n_f // d_f)
+                eng.set_cacqr_complete_inv(bool(ci)); eng.reset_info()
+                eng.cacqr_factor_3d(grid, a_f, q_f, r_f, variant, None, 1, 16); torch.cuda.synchronize()
+                report("3D CQR2 local Q vs reference (%s)" % tag, q_f.cpu().numpy(), fx["%s_Q_r%d" % (tag, rf)])
+                report("3D CQR2 local R vs reference (%s)" % tag, r_f.cpu().numpy(), fx["%s_R_r%d" % (tag, rf)])
+                ok = ok and same_input and eng.info() == 0
+                errs["3D CQR2 input bit-exact vs reference (%s)" % tag] = [1.0 if same_input else 0.0, 1.0]
+        except Exception as exc:  # noqa: BLE001 -- a check that could not run is reported, only a wrong number fails
+            errs["3D CQR2 vs reference fixture: not run"] = [0.0, 0.0]
+            if verbose and rank == 0:
+                print("3D CQR2 vs reference fixture not run: %s" % str(exc)[:200], flush=True)
+        finally:
+            eng.set_cacqr_complete_inv(True)
     for iters in (1, 2):
         q_loc, r_loc = colmajor(ml, l), colmajor(l, l)
         eng.reset_info()

@@ -28,7 +28,29 @@ def ceil_div(a, b):
     return -(-a // b)
 
 
+def gen_cacqr3d(tmp):
+    """3D CholeskyQR2 of the reference on 8 mini-MPI ranks, topo::rect(c = 2) = the 2x2x2 cube (cacqr.hpp:197-216 -> sweep_3d
+    :77-122), cholinv base case ReplicateComp, complete_inv = 1 and 0 (the latter goes through cacqr::solve, :46-73)."""
+    q = {}
+    m, n, c, d = 256, 32, 2, 2
+    for tag, ci in (("ci1", 1), ("ci0", 0)):
+        p = os.path.join(tmp, "q3" + tag)
+        line = run(8, ["cacqr", p, 2, m, n, c, ci, 1, 0, 0, 0, 2, 1], tmp)
+        q[tag + "_meta"] = np.array([8, 2, m, n, c, d, ci])
+        q[tag + "_line"] = np.array(line)
+        for r in range(8):
+            q["%s_A_r%d" % (tag, r)] = rd(p, r, "A", (m // d, n // c))
+            q["%s_Q_r%d" % (tag, r)] = rd(p, r, "Q", (m // d, n // c))
+            q["%s_R_r%d" % (tag, r)] = rd(p, r, "R", (n // c, n // c))
+    np.savez_compressed(os.path.join(HERE, "cacqr3d.npz"), **q)
+
+
 def main():
+    import sys
+    if "--only-cacqr3d" in sys.argv:
+        with tempfile.TemporaryDirectory() as tmp:
+            gen_cacqr3d(tmp)
+        return
     rng = np.random.default_rng(20261104)
     with tempfile.TemporaryDirectory() as tmp:
         # ---- generators -------------------------------------------------------------------------
@@ -56,6 +78,7 @@ def main():
                 q["%s_A_r%d" % (tag, r)] = rd(p, r, "A", (m // ranks, n))
                 q["%s_Q_r%d" % (tag, r)] = rd(p, r, "Q", (m // ranks, n))
         np.savez_compressed(os.path.join(HERE, "cacqr.npz"), **q)
+        gen_cacqr3d(tmp)
 
         # ---- cholinv ----------------------------------------------------------------------------
         c = {}

@@ -32,6 +32,39 @@ def test_grid_algorithms(world, n):
     _run_grid_check(world, n, 29540 + world)
 
 
+@pytest.mark.parametrize("tag", ["ci1", "ci0"])
+def test_cacqr_3d_vs_reference_fixture(engine, tag):
+    """cap_cacqr_factor_3d against the REFERENCE's 3D CholeskyQR2 (tests/golden/cacqr3d.npz: qr::cacqr::factor on the 2x2x2
+    cube, unmodified reference on 8 mini-MPI ranks; ci0 = cacqr::solve).  On one GPU the grid is 1x1x1 and the local block is
+    the assembled global matrix; Q and R are unique, so they must agree with the reference's assembled factors.  (At 8 ranks
+    capital_b200.checks.grid_small_check compares every rank's local blocks with the fixture directly.)"""
+    import torch
+    from capital_b200 import dist as cdist
+    from capital_b200.engine import colmajor, to_colmajor
+    from conftest import golden
+    q = golden("cacqr3d")
+    ranks, variant, m, n, c, d, ci = [int(v) for v in q[tag + "_meta"]]
+    blocks = {k: {} for k in "AQR"}
+    for r in range(ranks):
+        x, y, z = cdist.grid_coords(r, c, d)
+        if z == 0:
+            for k in "AQR":
+                blocks[k][(x, y)] = q["%s_%s_r%d" % (tag, k, r)]
+    Ag, Qg, Rg = (cdist.assemble_cyclic(blocks[k], d) for k in "AQR")
+    grid = cdist.Grid(engine, None, 1)
+    engine.set_cacqr_complete_inv(bool(ci))
+    try:
+        A = to_colmajor(Ag); Q = colmajor(m, n); R = colmajor(n, n)
+        engine.reset_info()
+        engine.cacqr_factor_3d(grid, A, Q, R, variant, None, 1, 16); torch.cuda.synchronize()
+        assert engine.info() == 0
+        assert relerr(np.triu(R.cpu().numpy()), np.triu(Rg)) <= TOL_FACTOR
+        assert relerr(Q.cpu().numpy(), Qg) <= TOL_FACTOR
+    finally:
+        engine.set_cacqr_complete_inv(True)
+        grid.close()
+
+
 def test_reference_engine_headers_bound_to_device(tmp_path):
     """integration/_build/engine_check = the reference's UNMODIFIED src/blas/{engine.h,interface.h} and
     src/lapack/{engine.h,interface.h} compiled (in the build container, integration/Makefile) with

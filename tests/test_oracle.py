@@ -48,6 +48,34 @@ def test_cacqr_matches_reference(tag):
     assert orc.qr_residual(A, Q, R) <= 1e-13 * n and orc.qr_orthogonality(Q) <= 1e-13 * n
 
 
+@pytest.mark.parametrize("tag", ["ci1", "ci0"])
+def test_cacqr_3d_reference_fixture(tag):
+    """tests/golden/cacqr3d.npz = the reference's 3D CholeskyQR2 on the 2x2x2 cube (topo::rect c = 2, 8 mini-MPI ranks;
+    ci0 goes through cacqr::solve).  Q and R of a full-rank matrix are unique, so the 1D restatement on the assembled matrix
+    must reproduce them; the inputs are the generator's (key = rank / c), bit for bit, and replicated over depth."""
+    from capital_b200 import dist as cdist
+    q = golden("cacqr3d")
+    ranks, variant, m, n, c, d, ci = [int(v) for v in q[tag + "_meta"]]
+    A, Q, R = {}, {}, {}
+    for r in range(ranks):
+        x, y, z = cdist.grid_coords(r, c, d)                       # topo::rect (topology.h:47-49) = z fastest, then x, then y
+        assert np.array_equal(q["%s_A_r%d" % (tag, r)], orc.distribute_random(n, m, x, y, c, d, r // c))
+        if z == 0:
+            A[(x, y)], Q[(x, y)], R[(x, y)] = (q["%s_%s_r%d" % (tag, k, r)] for k in "AQR")
+        else:
+            for k in "AQR":
+                assert np.array_equal(q["%s_%s_r%d" % (tag, k, r)], q["%s_%s_r%d" % (tag, k, r - z)])
+    Ag, Qg, Rg = (cdist.assemble_cyclic(b, d) for b in (A, Q, R))
+    rows = [Ag[p::4] for p in range(4)]                          # any row deal gives the same factors
+    qb, R1 = orc.cacqr_factor_1d(rows, 2)
+    Q1 = np.empty_like(Ag)
+    for p in range(4):
+        Q1[p::4] = qb[p]
+    assert relerr(np.triu(Rg), R1) <= TOL_FACTOR and relerr(Qg, Q1) <= TOL_FACTOR
+    assert np.all(np.tril(Rg, -1) == 0)
+    assert orc.qr_residual(Ag, Qg, np.triu(Rg)) <= 1e-13 * n and orc.qr_orthogonality(Qg) <= 1e-13 * n
+
+
 @pytest.mark.parametrize("tag", ["p1_ci1", "p1_ci0", "p8_ci1", "p8_ci0"])
 def test_cholinv_matches_reference(tag):
     c = golden("cholinv")
