@@ -271,9 +271,14 @@ def grid_small_check(eng, comm, world, rank, N=1024, verbose=False):
     finally:
         eng.set_cacqr_complete_inv(True)
     # every rank's LOCAL blocks against the reference itself: tests/golden/cacqr3d.npz holds qr::cacqr::factor of the unmodified
-    # reference on the 2x2x2 cube (8 mini-MPI ranks); the d = 2 face of worlds 4 (1x2x2) and 8 (2x2x2) holds the same blocks
+    # reference on the 2x2x2 cube (8 mini-MPI ranks); the d = 2 face of worlds 4 (1x2x2) and 8 (2x2x2) holds the same blocks.
+    # REPORTED, NOT DECIDING: this block was written after the round's multi-GPU budget was spent and has only run on one GPU
+    # (tests/test_gpu_grid.py::test_cacqr_3d_vs_reference_fixture, same fixture, 1x1x1 grid), so its numbers go into the result
+    # under "reference_fixture" without entering `ok`; the deciding 3D checks are the numpy comparisons above and below.
     fixture = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden", "cacqr3d.npz")
+    ref_fx = None
     if d == 2 and os.path.exists(fixture):
+        ref_fx, local = {}, {}
         try:
             fx = np.load(fixture)
             for tag in ("ci1", "ci0"):
@@ -284,16 +289,19 @@ def grid_small_check(eng, comm, world, rank, N=1024, verbose=False):
                 q_f, r_f = colmajor(m_f // d_f, n_f // d_f), colmajor(n_f // d_f, n_f // d_f)
                 eng.set_cacqr_complete_inv(bool(ci)); eng.reset_info()
                 eng.cacqr_factor_3d(grid, a_f, q_f, r_f, variant, None, 1, 16); torch.cuda.synchronize()
-                report("3D CQR2 local Q vs reference (%s)" % tag, q_f.cpu().numpy(), fx["%s_Q_r%d" % (tag, rf)])
-                report("3D CQR2 local R vs reference (%s)" % tag, r_f.cpu().numpy(), fx["%s_R_r%d" % (tag, rf)])
-                ok = ok and same_input and eng.info() == 0
-                errs["3D CQR2 input bit-exact vs reference (%s)" % tag] = [1.0 if same_input else 0.0, 1.0]
-        except Exception as exc:  # noqa: BLE001 -- a check that could not run is reported, only a wrong number fails
-            errs["3D CQR2 vs reference fixture: not run"] = [0.0, 0.0]
-            if verbose and rank == 0:
-                print("3D CQR2 vs reference fixture not run: %s" % str(exc)[:200], flush=True)
+                rel = lambda got, ref: float(np.linalg.norm(got - ref) / np.linalg.norm(ref))
+                local[tag] = (same_input, rel(q_f.cpu().numpy(), fx["%s_Q_r%d" % (tag, rf)]), rel(r_f.cpu().numpy(), fx["%s_R_r%d" % (tag, rf)]))
+        except Exception as exc:  # noqa: BLE001
+            ref_fx["error"] = "%s: %s" % (type(exc).__name__, str(exc)[:200])
         finally:
             eng.set_cacqr_complete_inv(True)
+        # the reductions over ranks sit OUTSIDE the try, in a fixed order every rank executes (no rank can be left alone in one)
+        for tag in ("ci1", "ci0"):
+            same_input, dq, dr = local.get(tag, (False, float("inf"), float("inf")))
+            fin = lambda v: v if v != float("inf") else None          # (JSON has no Infinity: a block that did not run gives null)
+            ref_fx[tag] = {"input_bit_exact": _all_ok(same_input), "dQ_local_max": fin(_max(dq)), "dR_local_max": fin(_max(dr))}
+            if verbose and rank == 0:
+                print("%-34s %s" % ("3D CQR2 local blocks vs reference (%s)" % tag, ref_fx[tag]), flush=True)
     for iters in (1, 2):
         q_loc, r_loc = colmajor(ml, l), colmajor(l, l)
         eng.reset_info()
@@ -324,7 +332,7 @@ def grid_small_check(eng, comm, world, rank, N=1024, verbose=False):
                     print("%-34s orth %.3e / %.3e  resid %.3e / %.3e %s" % ("validate 3D CQR2%s" % (" (damaged)" if damage else ""), o_dev, o_ref, r_dev, r_ref, "ok" if good else "FAIL"), flush=True)
     grid.close()
     return {"N": N, "grid": "%dx%dx%d" % (c, d, d), "worst_rel_err": max(v for v in errs.values() if not isinstance(v, list)) if errs else None,
-            "errors": errs, "ok": _all_ok(ok)}
+            "errors": errs, "reference_fixture": ref_fx, "ok": _all_ok(ok)}
 
 
 def cholinv_grid_block(eng, comm, world, rank, N, iters=2, peak=36.6, bc_global=2048):
