@@ -127,6 +127,14 @@ private:
 
 inline cap_handle_t handle() { return runtime::get().handle(); }
 
+// padXlen / padYlen of the reference's generators (src/matrix/structure.hpp:42-43,72-73,110-111): number of generated rows /
+// columns of a local block of `dim` when the grid does not divide the global dimension.  Pure arithmetic: tests/test_host_cpp.py
+// compiles it on the CPU and compares it with the oracle.
+inline int64_t pad_len(int64_t dim, int64_t global, int64_t local_p, int64_t grid_p) {
+  return ((global % grid_p != 0) && ((dim - 1) * grid_p + local_p >= global)) ? dim - 1 : dim;
+}
+inline int64_t local_dim(int64_t global, int64_t grid_p) { return (global + grid_p - 1) / grid_p; }   // matrix.hpp:142-150
+
 // What stands where the reference passes an MPI communicator (topology.h:18,69): the ranks of the runtime.
 struct world_t {};
 constexpr world_t WORLD{};
@@ -349,7 +357,7 @@ public:
   // Edge padding as in the reference (structure.hpp:42-43,72-73,110-111): when the grid does not divide a global dimension,
   // the ranks past the remainder hold one zero row / column at the end of their block and draw one value fewer per column.
   DimensionT pad_len(DimensionT dim, DimensionT global, int64_t local_p, int64_t grid_p) const {
-    return ((global % grid_p != 0) && ((dim - 1) * grid_p + local_p >= global)) ? dim - 1 : dim;
+    return (DimensionT)capital::pad_len((int64_t)dim, (int64_t)global, local_p, grid_p);
   }
   // structure.hpp:106-129: element t of the UNPADDED local block (column by column) = t-th drand48 value after srand48(key)
   void distribute_random(int64_t localPgridX, int64_t localPgridY, int64_t globalPgridX, int64_t globalPgridY, int64_t key) {
