@@ -21,7 +21,7 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", lr))
     eng = Engine(lr)
     comm = cdist.Comm(eng) if world > 1 else None
-    res = checks.grid_small_check(eng, comm, world, rank, N, verbose=True)
+    res = checks.grid_small_check(eng, comm, world, rank, N, verbose=True, reference_fixture=True)
     if rank == 0:
         print("GRID CHECK", "PASSED" if res["ok"] else "FAILED", "world", world, "grid", res["grid"], "N", N, flush=True)
     eng.close()
