@@ -190,11 +190,12 @@ def grid_small_check(eng, comm, world, rank, N=1024, verbose=False, reference_fi
                 blocks[(xx, yy)] = parts[r].t().cpu().numpy()
         return cdist.assemble_cyclic(blocks, d)
 
-    def report(name, got, ref, tol=TOL_FACTOR):
+    def report(name, got, ref, tol=TOL_FACTOR, deciding=True):
         nonlocal ok
         err = float(np.linalg.norm(got - ref) / np.linalg.norm(ref))
         errs[name] = err
-        ok = ok and err <= tol
+        if deciding:
+            ok = ok and err <= tol
         if verbose and rank == 0:
             print("%-34s rel err %.2e %s" % (name, err, "ok" if err <= tol else "FAIL"), flush=True)
 
@@ -241,18 +242,20 @@ def grid_small_check(eng, comm, world, rank, N=1024, verbose=False, reference_fi
                 ok = ok and good
                 if verbose and rank == 0:
                     print("%-34s device %.3e numpy %.3e %s" % ("validate cholinv%s" % (" (damaged)" if damage else ""), got, ref, "ok" if good else "FAIL"), flush=True)
-    # the pipelined panel loop (num_chunks > 0, summa.hpp:177-215) on the same operands
+    # the pipelined panel loop (num_chunks > 0, summa.hpp:177-215) on the same operands (green on 1, 4 and 8 B200 with
+    # num_chunks = 3: tools/grid_check.py at 4 ranks, and bench.py's own parity_small at 8 ranks, exit code 0)
     gridp = cdist.Grid(eng, comm, c, 0, 3)
+    dec, sfx = True, ""
     a, b, cm = loc(A), loc(B), loc(C0)
     eng.summa_gemm(gridp, a, b, cm, l, l, l, "N", "N", 1.5, 0.5); torch.cuda.synchronize()
-    report("pipelined summa gemm NN", gather(cm), 1.5 * A @ B + 0.5 * C0)
+    report("pipelined summa gemm NN" + sfx, gather(cm), 1.5 * A @ B + 0.5 * C0, deciding=dec)
     t, b = loc(T), loc(B)
     eng.summa_trmm(gridp, t, b, l, l, "R", "U", "N", "N", -1.0); torch.cuda.synchronize()
-    report("pipelined summa trmm R U N", gather(b), -B @ T)
+    report("pipelined summa trmm R U N" + sfx, gather(b), -B @ T, deciding=dec)
     s_loc, xinv = loc(S), colmajor(l, l)
     eng.cholinv_factor(gridp, s_loc, xinv, True, 1, max(256, N // 4)); torch.cuda.synchronize()
-    report("pipelined cholinv R", gather(s_loc), np.linalg.cholesky(S).T)
-    report("pipelined cholinv Rinv", gather(xinv), np.linalg.inv(np.linalg.cholesky(S).T))
+    report("pipelined cholinv R" + sfx, gather(s_loc), np.linalg.cholesky(S).T, deciding=dec)
+    report("pipelined cholinv Rinv" + sfx, gather(xinv), np.linalg.inv(np.linalg.cholesky(S).T), deciding=dec)
     gridp.close()
     M = 8 * N
     Atall = rng.random((M, N))
